@@ -1,0 +1,167 @@
+/*
+ * davis_b200.h -- C ABI of the B200 demodulation library (libdavis_b200.so).
+ *
+ * This is the drop-in boundary for rtldavis's demodulation hot path.  Each entry
+ * point names the reference interface it stands in for (paths relative to the
+ * rtldavis source tree).  Plain pointers and sizes only; no C++/torch types; no
+ * exception crosses the boundary.  Every function returns 0 (DAVIS_OK) or a
+ * negative DAVIS_E_* code; davis_last_error() gives the text for the last
+ * failure on a handle.  The caller owns every buffer it passes; the library
+ * owns the opaque handle and all device memory behind it.
+ *
+ * Batched model: one handle demodulates `n_streams` independent IQ streams.
+ * One davis_demod_u8() call feeds `n_blocks` consecutive blocks of every stream
+ * and yields exactly the packets that `n_blocks` successive calls of the
+ * reference's Demodulator.demodulate() would have returned for each stream,
+ * tagged with the call number.  A batch of one stream and one block is the
+ * reference's own call shape.
+ */
+#ifndef DAVIS_B200_H
+#define DAVIS_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define DAVIS_API __attribute__((visibility("default")))
+#else
+#define DAVIS_API
+#endif
+
+#define DAVIS_ABI_VERSION 1
+
+enum {
+    DAVIS_OK = 0,
+    DAVIS_E_INVAL = -1,     /* bad argument / unsupported configuration            */
+    DAVIS_E_SIZE = -2,      /* "Incompatible array sizes" (dsp.py:32-36,145-149)   */
+    DAVIS_E_CUDA = -3,      /* a CUDA runtime call failed                          */
+    DAVIS_E_NOMEM = -4,     /* host or device allocation failed                    */
+    DAVIS_E_OVERFLOW = -5,  /* hit or candidate buffer too small: nothing dropped
+                               silently, the call's results are withheld           */
+    DAVIS_E_STATE = -6      /* call sequence error (e.g. fetch with nothing queued) */
+};
+
+/* PacketConfig, src/rtldavis/dsp.py:101-125 (Go: dsp/dsp.go:172-218), as built by
+ * protocol.new_packet_config, src/rtldavis/protocol.py:68-76.  Derived sizes
+ * (sample_rate, preamble_length, packet_length, buffer_length) are recomputed by
+ * the library exactly as dsp.py:118-125 does.  Supported: symbol_length 14,
+ * preamble_symbols 16, packet_symbols 80, block_size a multiple of 8 and >= 256. */
+typedef struct davis_cfg {
+    int32_t bit_rate;          /* 19200                                             */
+    int32_t symbol_length;     /* samples per symbol, 14                            */
+    int32_t preamble_symbols;  /* 16                                                */
+    int32_t packet_symbols;    /* 80                                                */
+    uint32_t preamble;         /* sync pattern, first symbol in the MSB: 0xCB89     */
+    int32_t block_size;        /* samples per block: 8192 (Python) or 512 (Go)      */
+    int32_t max_blocks;        /* largest n_blocks a call will pass (>= 1)          */
+    int32_t max_hits;          /* capacity of the per-call packet buffer; 0 = auto  */
+    int32_t host_slots;        /* pipeline depth for host-memory input; 0 = auto    */
+    int32_t host_group;        /* streams per pipeline stage for host input; 0=auto */
+} davis_cfg;
+
+/* dsp.Packet, src/rtldavis/dsp.py:12-17 (Go: dsp/dsp.go:133-136), plus the
+ * verdict of the CRC gate in Parser.parse, src/rtldavis/protocol.py:290-300, and
+ * the mean the parser takes over `discriminated` (protocol.py:304-311). */
+typedef struct davis_hit {
+    int64_t position;     /* global sample index of the preamble in its stream      */
+    uint32_t stream;      /* stream the packet belongs to                           */
+    uint32_t call;        /* which demodulate() call of that stream returns it      */
+    int32_t index;        /* Packet.index (0..block_size inclusive)                 */
+    uint8_t data[10];     /* Packet.data, on-air bit order, MSB-first               */
+    uint8_t crc_ok;       /* 1 iff CRC-16(0x1021, init 0) of swapped bytes 2..9 = 0 */
+    uint8_t flags;        /* bit0: a decision bit was corrected by the fp64 re-check */
+    double rssi;          /* Packet.rssi, dsp.py:207-229                            */
+    double snr;           /* Packet.snr,  dsp.py:230-236                            */
+    double disc_mean;     /* mean(discriminated[index:index+224]), protocol.py:304-310 */
+} davis_hit;
+
+typedef struct davis_handle davis_handle;
+
+/* Counters of the most recent davis_demod_u8() call (all pipeline stages summed). */
+typedef struct davis_stats {
+    uint64_t samples;         /* complex samples demodulated (new blocks only)       */
+    uint64_t launches;        /* kernels launched                                    */
+    uint64_t candidates;      /* near-matches of the sync word in the fp32 bits      */
+    uint64_t confirmed;       /* preamble positions confirmed in fp64                */
+    uint64_t records;         /* (call, index) records produced, before dedupe       */
+    float demod_ms;           /* device time in the demodulation kernel              */
+    float search_ms;          /* device time in the sync search kernel               */
+    float finish_ms;          /* device time in confirm + slice/CRC + carry kernels  */
+    float total_ms;           /* first kernel start to last kernel end               */
+    uint64_t h2d_bytes;       /* bytes copied host->device by the call               */
+    uint64_t d2h_bytes;       /* bytes copied device->host by the fetch              */
+} davis_stats;
+
+DAVIS_API int davis_abi_version(void);
+
+/* Demodulator.__init__, src/rtldavis/dsp.py:127-137 (Go NewDemodulator,
+ * dsp/dsp.go:220-241), for n_streams independent streams on CUDA device `device`. */
+DAVIS_API int davis_create(const davis_cfg *cfg, int n_streams, int device, davis_handle **out);
+DAVIS_API int davis_destroy(davis_handle *h);
+
+/* Demodulator.reset, src/rtldavis/dsp.py:248-253 (Go: dsp/dsp.go:294-310).
+ * stream = -1 resets every stream (history, call counter). */
+DAVIS_API int davis_reset(davis_handle *h, int stream);
+
+/* Demodulator.demodulate, src/rtldavis/dsp.py:139-169 (Go: dsp/dsp.go:274-292),
+ * uint8 entry (ByteToCmplxLUT.execute, dsp.py:28-39), for n_blocks blocks of every
+ * stream.  `iq` is interleaved I,Q bytes; stream s starts at iq + s*stream_stride
+ * and supplies bytes_per_stream = n_blocks * 2 * block_size bytes (anything else
+ * is DAVIS_E_SIZE).  `iq` may be device memory (16-byte aligned, stride a multiple
+ * of 16; used in place, must stay valid until the fetch) or host memory (pinned
+ * for overlap; staged through the handle's pipeline).  Work is enqueued
+ * asynchronously; `cuda_stream` (a cudaStream_t, may be NULL) is the stream the
+ * caller's device input is ordered on. */
+DAVIS_API int davis_demod_u8(davis_handle *h, const uint8_t *iq, size_t bytes_per_stream,
+                   size_t stream_stride, int n_blocks, void *cuda_stream);
+
+/* Same for complex64 input (interleaved float re, im), the live pyrtlsdr entry,
+ * src/rtldavis/dsp.py:144-150.  samples_per_stream = n_blocks * block_size. */
+DAVIS_API int davis_demod_c64(davis_handle *h, const float *iq, size_t samples_per_stream,
+                    size_t stream_stride_bytes, int n_blocks, void *cuda_stream);
+
+/* Waits for the queued call and returns its packets: the concatenation, stream by
+ * stream and call by call, of what the reference returns (search order of
+ * dsp.py:171-188, the index <= block_size filter and per-call dedupe of
+ * dsp.py:190-205).  *n receives the number of packets; if it exceeds `cap` the
+ * function returns DAVIS_E_OVERFLOW with *n set and nothing copied, and may be
+ * called again with a larger buffer. */
+DAVIS_API int davis_fetch_hits(davis_handle *h, davis_hit *out, size_t cap, size_t *n);
+
+DAVIS_API int davis_get_stats(davis_handle *h, davis_stats *out);
+
+/* Verification taps (not on the product path).
+ * davis_debug_bits: the fp32 kernel's decision bits (Demodulator.quantized,
+ *   dsp.py:163-166) of the last call for one stream, one 0/1 byte per sample,
+ *   starting at global sample *first.
+ * davis_debug_disc: Demodulator.discriminated (dsp.py:133,162), the 2*block_size
+ *   float64 values the reference holds after the last call, recomputed in fp64.
+ * davis_debug_disc32: the fp32 kernel arithmetic's discriminator for the same
+ *   2*block_size samples (for the 1e-5 tolerance count). */
+DAVIS_API int davis_debug_bits(davis_handle *h, int stream, uint8_t *out, size_t cap,
+                     int64_t *first, size_t *n);
+DAVIS_API int davis_debug_disc(davis_handle *h, int stream, double *out, size_t cap);
+DAVIS_API int davis_debug_disc32(davis_handle *h, int stream, float *out, size_t cap);
+
+/* Pinned host memory for pipelined host input (cudaHostAlloc / cudaFreeHost). */
+DAVIS_API int davis_host_alloc(void **p, size_t bytes);
+DAVIS_API int davis_host_free(void *p);
+
+/* CRC.checksum, src/rtldavis/crc.py:19-26 (Go: crc/crc.go:37-44), and
+ * protocol.swap_bit_order, src/rtldavis/protocol.py:79-83, run on the device for
+ * `n` independent byte strings of `len` bytes each (parity taps for the CRC
+ * kernel; host buffers in and out). */
+DAVIS_API int davis_crc16_batch(const uint8_t *data, size_t n, size_t len, uint16_t init,
+                      uint16_t poly, int swap_bits, int device, uint16_t *out);
+
+DAVIS_API const char *davis_last_error(const davis_handle *h);
+DAVIS_API const char *davis_strerror(int code);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DAVIS_B200_H */

@@ -1,0 +1,583 @@
+// davis_capi.cu -- host side of libdavis_b200.so: the C ABI of include/davis_b200.h.
+//
+// Owns per-stream state (the carried tail of every stream and its call counter),
+// the pipeline stages used for host-memory input, and the host post-processing
+// that turns device records into the reference's per-call packet lists
+// (ordering of Demodulator._search, dsp.py:171-188; dedupe of _slice,
+// dsp.py:203-205).
+#include <algorithm>
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "davis_kernels.cuh"
+
+using namespace davis;
+
+namespace {
+
+struct Stage {
+    cudaStream_t st = nullptr;
+    uint8_t *staging = nullptr;  size_t staging_bytes = 0;
+    uint32_t *planes = nullptr;  size_t planes_words = 0;
+    Cand *cand = nullptr;        unsigned int cand_cap = 0;
+    Cand *conf = nullptr;        unsigned int conf_cap = 0;
+    Counters *ctr = nullptr;
+    int last_group = -1;
+    int tiles_alloc = 0;
+};
+
+struct Group {
+    int stage = 0, s0 = 0, ns = 0;
+    size_t hit_off = 0;  unsigned int hit_cap = 0;
+    cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+};
+
+}  // namespace
+
+struct davis_handle {
+    davis_cfg cfg{};
+    int n_streams = 0, device = 0;
+    int B = 0, W = 0, n_carry = 0, n_keep = 0;       // samples
+    size_t carry_stride = 0;
+    uint8_t *carry[2] = {nullptr, nullptr};
+    int cur = 0;
+    int64_t *d_blocks_done = nullptr;
+    std::vector<int64_t> h_blocks_done;
+    uint32_t pat_rev = 0;
+
+    std::vector<Stage> stages;
+    std::vector<Group> groups;            // groups of the queued call
+    std::vector<cudaEvent_t> event_pool;
+    davis_hit *d_hits = nullptr;  size_t d_hits_cap = 0;
+    Counters *h_ctr = nullptr;    size_t h_ctr_cap = 0;     // pinned, one per group
+
+    bool queued = false;
+    int queued_blocks = 0;
+    bool have_results = false;
+    std::vector<davis_hit> results;
+    davis_stats stats{};
+    int variant = 0;
+    std::string err;
+};
+
+namespace {
+
+int fail(davis_handle *h, int code, const std::string &msg) {
+    if (h) h->err = msg;
+    return code;
+}
+
+#define CU(call)                                                                          \
+    do {                                                                                  \
+        cudaError_t e_ = (call);                                                          \
+        if (e_ != cudaSuccess)                                                            \
+            return fail(h, e_ == cudaErrorMemoryAllocation ? DAVIS_E_NOMEM : DAVIS_E_CUDA, \
+                        std::string(#call) + ": " + cudaGetErrorString(e_));              \
+    } while (0)
+
+template <typename T>
+int grow(davis_handle *h, T **p, size_t *have, size_t want) {
+    if (*have >= want) return DAVIS_OK;
+    if (*p) CU(cudaFree(*p));
+    *p = nullptr; *have = 0;
+    CU(cudaMalloc((void **)p, want * sizeof(T)));
+    *have = want;
+    return DAVIS_OK;
+}
+
+int tiles_needed(int v_len) { return (v_len + TILE - 1) / TILE; }
+
+int prepare_stage(davis_handle *h, Stage &st, int ns, int n_blocks, size_t staging_bytes) {
+    const int v_len = h->n_carry + n_blocks * h->B;
+    int tiles = tiles_needed(v_len) + 1;                       // +1: the search reads tile j+1
+    tiles = (tiles + DEMOD_WARPS - 1) / DEMOD_WARPS * DEMOD_WARPS;
+    st.tiles_alloc = tiles;
+    int rc;
+    if ((rc = grow(h, &st.planes, &st.planes_words, (size_t)ns * tiles * PLANE_WORDS))) return rc;
+    if (staging_bytes && (rc = grow(h, &st.staging, &st.staging_bytes, staging_bytes))) return rc;
+    // expected near-matches: 17/65536 per sample position; allow 4x plus slack
+    const double positions = (double)ns * ((double)n_blocks + h->W) * h->B;
+    size_t want = (size_t)(positions * 17.0 / 65536.0 * 4.0) + 4096;
+    size_t have = st.cand_cap;
+    if ((rc = grow(h, &st.cand, &have, want))) return rc;
+    st.cand_cap = (unsigned int)have;
+    have = st.conf_cap;
+    if ((rc = grow(h, &st.conf, &have, want / 2))) return rc;
+    st.conf_cap = (unsigned int)have;
+    if (!st.ctr) CU(cudaMalloc((void **)&st.ctr, sizeof(Counters)));
+    if (!st.st) CU(cudaStreamCreateWithFlags(&st.st, cudaStreamNonBlocking));
+    return DAVIS_OK;
+}
+
+int get_event(davis_handle *h, cudaEvent_t *e) {
+    if (!h->event_pool.empty()) {
+        *e = h->event_pool.back();
+        h->event_pool.pop_back();
+        return DAVIS_OK;
+    }
+    CU(cudaEventCreate(e));
+    return DAVIS_OK;
+}
+
+void release_groups(davis_handle *h) {
+    for (auto &g : h->groups)
+        for (auto &e : g.ev)
+            if (e) { h->event_pool.push_back(e); e = nullptr; }
+    h->groups.clear();
+}
+
+// Enqueue every kernel of one group of streams on `st`.
+int run_group(davis_handle *h, Stage &stage, Group &g, int gi, const uint8_t *dev_input,
+              size_t input_stride, int n_blocks, cudaStream_t st) {
+    View vw;
+    vw.carry = h->carry[h->cur] + (size_t)g.s0 * h->carry_stride + 2 * (size_t)(h->n_keep - h->n_carry);
+    vw.input = dev_input;
+    vw.carry_stride = h->carry_stride;
+    vw.input_stride = input_stride;
+    vw.blocks_done = h->d_blocks_done + g.s0;
+    vw.n_carry = h->n_carry;
+    vw.n_new = n_blocks * h->B;
+    vw.block = h->B;
+    vw.window_blocks = h->W;
+    vw.stream0 = g.s0;
+
+    SearchParams sp;
+    sp.pat_rev = h->pat_rev;
+    sp.v_lo = HALO;
+    sp.v_hi = HALO + n_blocks * h->B;
+    sp.tiles = sp.v_hi / TILE + 1;
+    sp.tiles_alloc = stage.tiles_alloc;
+    sp.n_streams = g.ns;
+    sp.cand_cap = stage.cand_cap;
+    sp.conf_cap = stage.conf_cap;
+    sp.hit_cap = g.hit_cap;
+
+    CU(cudaMemsetAsync(stage.ctr, 0, sizeof(Counters), st));
+    CU(cudaEventRecord(g.ev[0], st));
+    launch_demod(vw, stage.planes, g.ns, stage.tiles_alloc, h->variant, nullptr, 0, st);
+    CU(cudaEventRecord(g.ev[1], st));
+    launch_search(stage.planes, sp, stage.cand, stage.ctr, st);
+    CU(cudaEventRecord(g.ev[2], st));
+    launch_precheck(vw, sp, stage.cand, stage.conf, stage.ctr, st);
+    launch_confirm(vw, sp, stage.planes, stage.conf, h->d_hits + g.hit_off, stage.ctr, n_blocks, st);
+    launch_carry(h->carry[h->cur] + (size_t)g.s0 * h->carry_stride,
+                 h->carry[h->cur ^ 1] + (size_t)g.s0 * h->carry_stride, h->carry_stride, h->n_keep,
+                 dev_input, input_stride, n_blocks * h->B, g.ns, h->d_blocks_done + g.s0, n_blocks,
+                 st);
+    CU(cudaEventRecord(g.ev[3], st));
+    CU(cudaMemcpyAsync(&h->h_ctr[gi], stage.ctr, sizeof(Counters), cudaMemcpyDeviceToHost, st));
+    CU(cudaEventRecord(g.ev[4], st));
+    CU(cudaGetLastError());
+    stage.last_group = gi;
+    h->stats.launches += 4 + (uint64_t)((g.ns + 65534) / 65535);
+    return DAVIS_OK;
+}
+
+bool hit_less(const davis_hit &a, const davis_hit &b) {
+    if (a.stream != b.stream) return a.stream < b.stream;
+    if (a.call != b.call) return a.call < b.call;
+    const int pa = a.index % SPS, pb = b.index % SPS;     // dsp.py:175: offset-major
+    if (pa != pb) return pa < pb;
+    return a.index < b.index;
+}
+
+}  // namespace
+
+extern "C" {
+
+int davis_abi_version(void) { return DAVIS_ABI_VERSION; }
+
+const char *davis_strerror(int code) {
+    switch (code) {
+    case DAVIS_OK: return "ok";
+    case DAVIS_E_INVAL: return "invalid argument or unsupported configuration";
+    case DAVIS_E_SIZE: return "Incompatible array sizes";
+    case DAVIS_E_CUDA: return "CUDA runtime error";
+    case DAVIS_E_NOMEM: return "out of memory";
+    case DAVIS_E_OVERFLOW: return "result buffer too small";
+    case DAVIS_E_STATE: return "call sequence error";
+    default: return "unknown error";
+    }
+}
+
+const char *davis_last_error(const davis_handle *h) { return h ? h->err.c_str() : ""; }
+
+int davis_create(const davis_cfg *cfg, int n_streams, int device, davis_handle **out) {
+    if (!cfg || !out || n_streams < 1) return DAVIS_E_INVAL;
+    *out = nullptr;
+    if (cfg->symbol_length != SPS || cfg->preamble_symbols != PRE_SYMS ||
+        cfg->packet_symbols != PKT_SYMS || cfg->block_size < 256 || cfg->block_size % 8 ||
+        cfg->max_blocks < 1 || cfg->preamble > 0xFFFFu)
+        return DAVIS_E_INVAL;
+    int count = 0;
+    if (cudaGetDeviceCount(&count) != cudaSuccess || device < 0 || device >= count)
+        return DAVIS_E_CUDA;
+    davis_handle *h = new (std::nothrow) davis_handle;
+    if (!h) return DAVIS_E_NOMEM;
+    h->cfg = *cfg;
+    h->n_streams = n_streams;
+    h->device = device;
+    h->B = cfg->block_size;
+    h->W = (PKT_SYMS * SPS) / h->B + 2;                          // dsp.py:123-125
+    h->n_carry = (h->W - 1) * h->B + HALO;
+    h->n_keep = std::max(h->W - 1, 2) * h->B + HALO;             // also covers `discriminated`
+    h->carry_stride = 2 * (size_t)h->n_keep;
+    for (int i = 0; i < PRE_SYMS; i++)                           // symbol 0 is the MSB
+        h->pat_rev |= ((cfg->preamble >> (PRE_SYMS - 1 - i)) & 1u) << i;
+    h->h_blocks_done.assign(n_streams, 0);
+    const char *var = getenv("DAVIS_DEMOD_VARIANT");
+    h->variant = var ? atoi(var) : 0;
+
+    auto bail = [&](int rc) { davis_destroy(h); return rc; };
+    if (cudaSetDevice(device) != cudaSuccess) return bail(DAVIS_E_CUDA);
+    for (int i = 0; i < 2; i++) {
+        if (cudaMalloc((void **)&h->carry[i], h->carry_stride * n_streams) != cudaSuccess)
+            return bail(DAVIS_E_NOMEM);
+        cudaMemset(h->carry[i], 0, h->carry_stride * n_streams);
+    }
+    if (cudaMalloc((void **)&h->d_blocks_done, sizeof(int64_t) * n_streams) != cudaSuccess)
+        return bail(DAVIS_E_NOMEM);
+    cudaMemset(h->d_blocks_done, 0, sizeof(int64_t) * n_streams);
+    int slots = cfg->host_slots > 0 ? cfg->host_slots : 3;
+    h->stages.resize(slots);
+    if (cudaDeviceSynchronize() != cudaSuccess) return bail(DAVIS_E_CUDA);
+    *out = h;
+    return DAVIS_OK;
+}
+
+int davis_destroy(davis_handle *h) {
+    if (!h) return DAVIS_OK;
+    cudaSetDevice(h->device);
+    cudaDeviceSynchronize();
+    release_groups(h);
+    for (auto e : h->event_pool) cudaEventDestroy(e);
+    for (auto &s : h->stages) {
+        if (s.staging) cudaFree(s.staging);
+        if (s.planes) cudaFree(s.planes);
+        if (s.cand) cudaFree(s.cand);
+        if (s.conf) cudaFree(s.conf);
+        if (s.ctr) cudaFree(s.ctr);
+        if (s.st) cudaStreamDestroy(s.st);
+    }
+    for (int i = 0; i < 2; i++) if (h->carry[i]) cudaFree(h->carry[i]);
+    if (h->d_blocks_done) cudaFree(h->d_blocks_done);
+    if (h->d_hits) cudaFree(h->d_hits);
+    if (h->h_ctr) cudaFreeHost(h->h_ctr);
+    delete h;
+    return DAVIS_OK;
+}
+
+int davis_reset(davis_handle *h, int stream) {
+    if (!h || stream < -1 || stream >= h->n_streams) return fail(h, DAVIS_E_INVAL, "bad stream");
+    CU(cudaSetDevice(h->device));
+    CU(cudaDeviceSynchronize());
+    if (stream < 0) {
+        std::fill(h->h_blocks_done.begin(), h->h_blocks_done.end(), 0);
+        CU(cudaMemset(h->d_blocks_done, 0, sizeof(int64_t) * h->n_streams));
+    } else {
+        h->h_blocks_done[stream] = 0;
+        CU(cudaMemset(h->d_blocks_done + stream, 0, sizeof(int64_t)));
+    }
+    h->queued = false;
+    h->have_results = false;
+    release_groups(h);
+    return DAVIS_OK;
+}
+
+int davis_demod_u8(davis_handle *h, const uint8_t *iq, size_t bytes_per_stream,
+                   size_t stream_stride, int n_blocks, void *cuda_stream) {
+    if (!h) return DAVIS_E_INVAL;
+    if (!iq || n_blocks < 1) return fail(h, DAVIS_E_INVAL, "null input or n_blocks < 1");
+    if (n_blocks > h->cfg.max_blocks)
+        return fail(h, DAVIS_E_INVAL, "n_blocks exceeds davis_cfg.max_blocks");
+    if (bytes_per_stream != (size_t)n_blocks * 2 * h->B)
+        return fail(h, DAVIS_E_SIZE, "Incompatible array sizes");
+    if (h->n_streams > 1 && stream_stride < bytes_per_stream)
+        return fail(h, DAVIS_E_SIZE, "stream_stride smaller than bytes_per_stream");
+    if (h->queued) return fail(h, DAVIS_E_STATE, "previous call not fetched");
+    CU(cudaSetDevice(h->device));
+
+    cudaPointerAttributes attr;
+    bool on_device = false;
+    if (cudaPointerGetAttributes(&attr, iq) == cudaSuccess)
+        on_device = attr.type == cudaMemoryTypeDevice || attr.type == cudaMemoryTypeManaged;
+    else
+        cudaGetLastError();
+    if (on_device && (((uintptr_t)iq & 15) || (h->n_streams > 1 && (stream_stride & 15))))
+        return fail(h, DAVIS_E_INVAL, "device input must be 16-byte aligned with a 16-byte stride");
+
+    release_groups(h);
+    h->have_results = false;
+    h->stats = davis_stats{};
+    h->stats.samples = (uint64_t)h->n_streams * n_blocks * h->B;
+
+    // split into groups
+    int per_group = h->n_streams;
+    if (!on_device) {
+        per_group = h->cfg.host_group > 0 ? h->cfg.host_group : 0;
+        if (per_group <= 0) {                       // ~64 MiB of input per pipeline stage
+            per_group = (int)std::max<size_t>(1, ((size_t)64 << 20) / bytes_per_stream);
+        }
+        per_group = std::min(per_group, h->n_streams);
+    }
+    const int n_groups = (h->n_streams + per_group - 1) / per_group;
+    h->groups.resize(n_groups);
+    size_t hit_total = 0;
+    for (int gi = 0; gi < n_groups; gi++) {
+        Group &g = h->groups[gi];
+        g.stage = on_device ? 0 : gi % (int)h->stages.size();
+        g.s0 = gi * per_group;
+        g.ns = std::min(per_group, h->n_streams - g.s0);
+        size_t cap = h->cfg.max_hits > 0 ? (size_t)h->cfg.max_hits
+                                         : 1024 + (size_t)g.ns * ((size_t)n_blocks + h->W) * 4;
+        g.hit_cap = (unsigned int)std::min<size_t>(cap, 0x7FFFFFFFu);
+        g.hit_off = hit_total;
+        hit_total += g.hit_cap;
+        for (auto &e : g.ev) { int rc = get_event(h, &e); if (rc) return rc; }
+    }
+    int rc;
+    if ((rc = grow(h, &h->d_hits, &h->d_hits_cap, hit_total))) return rc;
+    if (h->h_ctr_cap < (size_t)n_groups) {
+        if (h->h_ctr) CU(cudaFreeHost(h->h_ctr));
+        h->h_ctr = nullptr; h->h_ctr_cap = 0;
+        CU(cudaHostAlloc((void **)&h->h_ctr, sizeof(Counters) * n_groups, cudaHostAllocDefault));
+        h->h_ctr_cap = n_groups;
+    }
+
+    for (int gi = 0; gi < n_groups; gi++) {
+        Group &g = h->groups[gi];
+        Stage &stage = h->stages[g.stage];
+        const size_t stage_bytes = on_device ? 0 : (size_t)per_group * bytes_per_stream;
+        if ((rc = prepare_stage(h, stage, on_device ? h->n_streams : per_group, n_blocks, stage_bytes)))
+            return rc;
+        cudaStream_t st = stage.st;
+        const uint8_t *dev_in;
+        size_t dev_stride;
+        if (on_device) {
+            if (cuda_stream) st = (cudaStream_t)cuda_stream;
+            dev_in = iq;
+            dev_stride = stream_stride;
+        } else {
+            CU(cudaMemcpy2DAsync(stage.staging, bytes_per_stream, iq + (size_t)g.s0 * stream_stride,
+                                 stream_stride, bytes_per_stream, g.ns, cudaMemcpyHostToDevice, st));
+            h->stats.h2d_bytes += (uint64_t)bytes_per_stream * g.ns;
+            dev_in = stage.staging;
+            dev_stride = bytes_per_stream;
+        }
+        if ((rc = run_group(h, stage, g, gi, dev_in, dev_stride, n_blocks, st))) return rc;
+    }
+    h->cur ^= 1;
+    for (auto &b : h->h_blocks_done) b += n_blocks;
+    h->queued = true;
+    h->queued_blocks = n_blocks;
+    return DAVIS_OK;
+}
+
+int davis_demod_c64(davis_handle *h, const float *, size_t, size_t, int, void *) {
+    return fail(h, DAVIS_E_INVAL, "complex64 input is not implemented yet");
+}
+
+int davis_fetch_hits(davis_handle *h, davis_hit *out, size_t cap, size_t *n) {
+    if (!h || !n) return DAVIS_E_INVAL;
+    CU(cudaSetDevice(h->device));
+    if (h->queued) {
+        h->results.clear();
+        float demod = 0, search = 0, finish = 0;
+        for (size_t gi = 0; gi < h->groups.size(); gi++) {
+            Group &g = h->groups[gi];
+            CU(cudaEventSynchronize(g.ev[4]));
+            const Counters c = h->h_ctr[gi];
+            float ms;
+            CU(cudaEventElapsedTime(&ms, g.ev[0], g.ev[1])); demod += ms;
+            CU(cudaEventElapsedTime(&ms, g.ev[1], g.ev[2])); search += ms;
+            CU(cudaEventElapsedTime(&ms, g.ev[2], g.ev[3])); finish += ms;
+            h->stats.candidates += c.n_cand;
+            h->stats.confirmed += c.n_conf;
+            h->stats.records += c.n_hit;
+            if (c.overflow) {
+                h->queued = false;
+                char msg[160];
+                snprintf(msg, sizeof msg,
+                         "device buffer overflow (mask %u): cand %u conf %u hits %u; raise max_hits",
+                         c.overflow, c.n_cand, c.n_conf, c.n_hit);
+                return fail(h, DAVIS_E_OVERFLOW, msg);
+            }
+            const size_t at = h->results.size();
+            h->results.resize(at + c.n_hit);
+            if (c.n_hit) {
+                CU(cudaMemcpy(h->results.data() + at, h->d_hits + g.hit_off,
+                              sizeof(davis_hit) * c.n_hit, cudaMemcpyDeviceToHost));
+                h->stats.d2h_bytes += sizeof(davis_hit) * c.n_hit;
+            }
+            h->stats.d2h_bytes += sizeof(Counters);
+        }
+        h->stats.demod_ms = demod;
+        h->stats.search_ms = search;
+        h->stats.finish_ms = finish;
+        if (!h->groups.empty()) {
+            float first_to_last = 0;
+            // stages overlap; report the span of the slowest single group chain instead
+            for (auto &g : h->groups) {
+                float ms;
+                CU(cudaEventElapsedTime(&ms, g.ev[0], g.ev[3]));
+                first_to_last += ms;
+            }
+            h->stats.total_ms = first_to_last;
+        }
+        // reference order + per-call dedupe on the payload (dsp.py:203-205)
+        std::sort(h->results.begin(), h->results.end(), hit_less);
+        size_t w = 0, call_begin = 0;
+        for (size_t i = 0; i < h->results.size(); i++) {
+            const davis_hit &r = h->results[i];
+            if (w == 0 || h->results[call_begin].stream != r.stream ||
+                h->results[call_begin].call != r.call)
+                call_begin = w;
+            bool dup = false;
+            for (size_t j = call_begin; j < w && !dup; j++)
+                dup = !memcmp(h->results[j].data, r.data, PKT_BYTES);
+            if (!dup) h->results[w++] = r;
+        }
+        h->results.resize(w);
+        h->queued = false;
+        h->have_results = true;
+    } else if (!h->have_results) {
+        return fail(h, DAVIS_E_STATE, "nothing queued");
+    }
+    *n = h->results.size();
+    if (*n > cap) return fail(h, DAVIS_E_OVERFLOW, "caller buffer smaller than the packet count");
+    if (*n) memcpy(out, h->results.data(), sizeof(davis_hit) * *n);
+    return DAVIS_OK;
+}
+
+int davis_get_stats(davis_handle *h, davis_stats *out) {
+    if (!h || !out) return DAVIS_E_INVAL;
+    *out = h->stats;
+    return DAVIS_OK;
+}
+
+int davis_debug_bits(davis_handle *h, int stream, uint8_t *out, size_t cap, int64_t *first,
+                     size_t *n) {
+    if (!h || !out || !first || !n || stream < 0 || stream >= h->n_streams)
+        return fail(h, DAVIS_E_INVAL, "bad argument");
+    if (h->queued || h->groups.empty()) return fail(h, DAVIS_E_STATE, "fetch the call first");
+    CU(cudaSetDevice(h->device));
+    for (size_t gi = 0; gi < h->groups.size(); gi++) {
+        const Group &g = h->groups[gi];
+        if (stream < g.s0 || stream >= g.s0 + g.ns) continue;
+        const Stage &st = h->stages[g.stage];
+        if (st.last_group != (int)gi)
+            return fail(h, DAVIS_E_STATE, "planes of that stream were recycled by a later group");
+        const int v_len = h->n_carry + h->queued_blocks * h->B;
+        const size_t count = (size_t)v_len - HALO;
+        *n = count;
+        *first = (h->h_blocks_done[stream] - h->queued_blocks) * (int64_t)h->B - h->n_carry + HALO;
+        if (count > cap) return fail(h, DAVIS_E_OVERFLOW, "bit buffer too small");
+        std::vector<uint32_t> words((size_t)st.tiles_alloc * PLANE_WORDS);
+        CU(cudaMemcpy(words.data(),
+                      st.planes + (size_t)(stream - g.s0) * st.tiles_alloc * PLANE_WORDS,
+                      words.size() * 4, cudaMemcpyDeviceToHost));
+        for (size_t i = 0; i < count; i++) {
+            const size_t v = i + HALO, sym = v / SPS, ph = v % SPS;
+            out[i] = (uint8_t)((words[(sym >> 5) * PLANE_WORDS + ph] >> (sym & 31)) & 1u);
+        }
+        return DAVIS_OK;
+    }
+    return fail(h, DAVIS_E_STATE, "stream not in the last call");
+}
+
+static int debug_view(davis_handle *h, View *vw) {
+    vw->carry = h->carry[h->cur];
+    vw->input = nullptr;
+    vw->carry_stride = h->carry_stride;
+    vw->input_stride = 0;
+    vw->blocks_done = h->d_blocks_done;
+    vw->n_carry = h->n_keep;
+    vw->n_new = 0;
+    vw->block = h->B;
+    vw->window_blocks = h->W;
+    vw->stream0 = 0;
+    return DAVIS_OK;
+}
+
+int davis_debug_disc(davis_handle *h, int stream, double *out, size_t cap) {
+    if (!h || !out || stream < 0 || stream >= h->n_streams) return fail(h, DAVIS_E_INVAL, "bad argument");
+    if (cap < (size_t)2 * h->B) return fail(h, DAVIS_E_OVERFLOW, "need 2*block_size doubles");
+    if (h->queued) return fail(h, DAVIS_E_STATE, "fetch the call first");
+    CU(cudaSetDevice(h->device));
+    CU(cudaDeviceSynchronize());
+    View vw;
+    debug_view(h, &vw);
+    double *d = nullptr;
+    CU(cudaMalloc((void **)&d, sizeof(double) * 2 * h->B));
+    launch_exact_disc(vw, stream, h->n_keep - 2 * h->B, 2 * h->B, d, 0);
+    cudaError_t e = cudaMemcpy(out, d, sizeof(double) * 2 * h->B, cudaMemcpyDeviceToHost);
+    cudaFree(d);
+    if (e != cudaSuccess) return fail(h, DAVIS_E_CUDA, cudaGetErrorString(e));
+    return DAVIS_OK;
+}
+
+int davis_debug_disc32(davis_handle *h, int stream, float *out, size_t cap) {
+    if (!h || !out || stream < 0 || stream >= h->n_streams) return fail(h, DAVIS_E_INVAL, "bad argument");
+    if (cap < (size_t)2 * h->B) return fail(h, DAVIS_E_OVERFLOW, "need 2*block_size floats");
+    if (h->queued) return fail(h, DAVIS_E_STATE, "fetch the call first");
+    CU(cudaSetDevice(h->device));
+    CU(cudaDeviceSynchronize());
+    View vw;
+    debug_view(h, &vw);
+    vw.carry += (size_t)stream * h->carry_stride;
+    vw.blocks_done += stream;
+    int tiles = tiles_needed(h->n_keep) + 1;
+    tiles = (tiles + DEMOD_WARPS - 1) / DEMOD_WARPS * DEMOD_WARPS;
+    uint32_t *planes = nullptr;
+    float *d = nullptr;
+    const size_t n_disc = (size_t)tiles * TILE;
+    CU(cudaMalloc((void **)&planes, sizeof(uint32_t) * tiles * PLANE_WORDS));
+    if (cudaMalloc((void **)&d, sizeof(float) * n_disc) != cudaSuccess) {
+        cudaFree(planes);
+        return fail(h, DAVIS_E_NOMEM, "cudaMalloc");
+    }
+    launch_demod(vw, planes, 1, tiles, 0, d, n_disc, 0);
+    cudaError_t e = cudaMemcpy(out, d + (h->n_keep - 2 * h->B), sizeof(float) * 2 * h->B,
+                               cudaMemcpyDeviceToHost);
+    cudaFree(planes);
+    cudaFree(d);
+    if (e != cudaSuccess) return fail(h, DAVIS_E_CUDA, cudaGetErrorString(e));
+    return DAVIS_OK;
+}
+
+int davis_host_alloc(void **p, size_t bytes) {
+    if (!p) return DAVIS_E_INVAL;
+    return cudaHostAlloc(p, bytes, cudaHostAllocDefault) == cudaSuccess ? DAVIS_OK : DAVIS_E_NOMEM;
+}
+
+int davis_host_free(void *p) {
+    return cudaFreeHost(p) == cudaSuccess ? DAVIS_OK : DAVIS_E_CUDA;
+}
+
+int davis_crc16_batch(const uint8_t *data, size_t n, size_t len, uint16_t init, uint16_t poly,
+                      int swap_bits, int device, uint16_t *out) {
+    if ((!data && n * len) || !out) return DAVIS_E_INVAL;
+    if (n == 0) return DAVIS_OK;
+    if (cudaSetDevice(device) != cudaSuccess) return DAVIS_E_CUDA;
+    uint8_t *d_in = nullptr;
+    uint16_t *d_out = nullptr;
+    int rc = DAVIS_OK;
+    if (cudaMalloc((void **)&d_in, n * len + 1) != cudaSuccess ||
+        cudaMalloc((void **)&d_out, n * sizeof(uint16_t)) != cudaSuccess)
+        rc = DAVIS_E_NOMEM;
+    if (!rc && n * len && cudaMemcpy(d_in, data, n * len, cudaMemcpyHostToDevice) != cudaSuccess)
+        rc = DAVIS_E_CUDA;
+    if (!rc) {
+        launch_crc16(d_in, n, len, init, poly, swap_bits, d_out, 0);
+        if (cudaMemcpy(out, d_out, n * sizeof(uint16_t), cudaMemcpyDeviceToHost) != cudaSuccess)
+            rc = DAVIS_E_CUDA;
+    }
+    if (d_in) cudaFree(d_in);
+    if (d_out) cudaFree(d_out);
+    return rc;
+}
+
+}  // extern "C"

@@ -1,0 +1,52 @@
+// davis_kernels.cuh -- kernel declarations and the records they exchange.
+#pragma once
+#include "davis_device.cuh"
+#include "../../include/davis_b200.h"
+
+namespace davis {
+
+// A position where the fp32 decision bits match the sync word with at most one
+// disagreeing symbol.  `miss` is the disagreeing symbol (0..15) or -1.
+struct Cand {
+    uint32_t stream;   // local to the pipeline stage
+    int32_t v;         // index into the call's virtual sample sequence
+    int32_t miss;
+    uint32_t pad;
+};
+
+// Device-side counters of one pipeline stage (zeroed before every call).
+struct Counters {
+    unsigned int n_cand;       // entries appended to the candidate list
+    unsigned int n_conf;       // entries appended to the confirmed list
+    unsigned int n_hit;        // records appended to the hit buffer
+    unsigned int overflow;     // bit0 cand, bit1 conf, bit2 hit
+};
+
+struct SearchParams {
+    uint32_t pat_rev;          // sync word with symbol 0 in bit 0
+    int v_lo, v_hi;            // inclusive range of reportable positions
+    int tiles;                 // tiles per stream that hold decided bits
+    int tiles_alloc;           // tiles per stream in the plane buffer
+    int n_streams;
+    unsigned int cand_cap, conf_cap, hit_cap;
+};
+
+constexpr int DEMOD_WARPS = 8;
+
+void launch_demod(const View &vw, uint32_t *planes, int n_streams, int tiles_alloc, int variant,
+                  float *disc_out, size_t disc_stride, cudaStream_t st);
+void launch_search(const uint32_t *planes, const SearchParams &sp, Cand *cand, Counters *ctr,
+                   cudaStream_t st);
+void launch_precheck(const View &vw, const SearchParams &sp, const Cand *cand, Cand *conf,
+                     Counters *ctr, cudaStream_t st);
+void launch_confirm(const View &vw, const SearchParams &sp, const uint32_t *planes,
+                    const Cand *conf, davis_hit *hits, Counters *ctr, int n_blocks,
+                    cudaStream_t st);
+void launch_carry(const uint8_t *carry_old, uint8_t *carry_new, size_t carry_stride, int keep,
+                  const uint8_t *input, size_t input_stride, int n_new, int n_streams,
+                  int64_t *blocks_done, int n_blocks, cudaStream_t st);
+void launch_exact_disc(const View &vw, int stream, int v0, int n, double *out, cudaStream_t st);
+void launch_crc16(const uint8_t *data, size_t n, size_t len, uint16_t init, uint16_t poly,
+                  int swap_bits, uint16_t *out, cudaStream_t st);
+
+}  // namespace davis

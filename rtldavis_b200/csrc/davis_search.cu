@@ -1,0 +1,336 @@
+// davis_search.cu -- sync-word search over the decision-bit planes, fp64
+// confirmation, packet slicing, CRC-16 and per-call record generation.
+//
+// Replaces Demodulator._search (src/rtldavis/dsp.py:171-188; Go Pack/Search,
+// dsp/dsp.go:105-131 + dsp/search.go:104-119), Demodulator._slice
+// (dsp.py:190-246; Go dsp/dsp.go:138-169) and the CRC gate of Parser.parse
+// (src/rtldavis/protocol.py:290-300 with crc.py:19-42 and protocol.py:79-83).
+#include "davis_kernels.cuh"
+
+namespace davis {
+
+// ---------------------------------------------------------------------------
+// k_search: one thread per (stream, tile, phase) word of 32 symbols.
+// A position is a candidate when the 16 symbols starting there differ from the
+// sync word in at most one symbol.  By pigeonhole such a window matches the
+// first or the second half of the word exactly, so the word-parallel part only
+// computes two 8-literal AND chains; the rare survivors are checked with popc.
+// The one-symbol slack exists because the planes come from fp32 arithmetic: a
+// true match (in the reference's float64) with one marginal fp32 sign must not
+// be lost.  k_precheck settles such positions in fp64.
+// ---------------------------------------------------------------------------
+constexpr int SEARCH_THREADS = 256;
+constexpr int STAGE = 128;   // per-block staging slots for found candidates
+
+template <typename T>
+__device__ __forceinline__ void block_flush(T *stage, int n_staged, T *out, unsigned int *counter,
+                                            unsigned int cap, unsigned int *overflow,
+                                            unsigned int flag, unsigned int *s_base) {
+    __syncthreads();
+    if (n_staged == 0) return;
+    if (threadIdx.x == 0) *s_base = atomicAdd(counter, (unsigned int)n_staged);
+    __syncthreads();
+    const unsigned int base = *s_base;
+    for (int i = threadIdx.x; i < n_staged; i += blockDim.x) {
+        if (base + i < cap) out[base + i] = stage[i];
+        else atomicOr(overflow, flag);
+    }
+}
+
+__global__ void __launch_bounds__(SEARCH_THREADS)
+k_search(const uint32_t *__restrict__ planes, SearchParams sp, Cand *__restrict__ cand,
+         Counters *ctr) {
+    __shared__ Cand stage[STAGE];
+    __shared__ int n_stage;
+    __shared__ unsigned int s_base;
+    if (threadIdx.x == 0) n_stage = 0;
+    __syncthreads();
+
+    const long long word = (long long)blockIdx.x * SEARCH_THREADS + threadIdx.x;
+    const int p = (int)(word & (PLANE_WORDS - 1));
+    const long long tile_lin = word >> 4;
+    const int s = (int)(tile_lin / sp.tiles);
+    const int j = (int)(tile_lin - (long long)s * sp.tiles);
+
+    if (s < sp.n_streams && p < SPS) {
+        const uint32_t *base = planes + ((size_t)s * sp.tiles_alloc + j) * PLANE_WORDS + p;
+        const uint32_t w0 = __ldg(base), w1 = __ldg(base + PLANE_WORDS);
+        uint32_t lo = 0xFFFFFFFFu, hi = 0xFFFFFFFFu;
+#pragma unroll
+        for (int i = 0; i < 8; i++) {
+            const uint32_t x = __funnelshift_r(w0, w1, i);
+            const uint32_t y = __funnelshift_r(w0, w1, i + 8);
+            lo &= ((sp.pat_rev >> i) & 1u) ? x : ~x;
+            hi &= ((sp.pat_rev >> (i + 8)) & 1u) ? y : ~y;
+        }
+        uint32_t m = lo | hi;
+        while (m) {
+            const int l = __ffs(m) - 1;
+            m &= m - 1;
+            const int v = SPS * (32 * j + l) + p;
+            if (v < sp.v_lo || v > sp.v_hi) continue;
+            const uint32_t win = __funnelshift_r(w0, w1, l) & 0xFFFFu;
+            const uint32_t diff = win ^ sp.pat_rev;
+            if (__popc(diff) > 1) continue;
+            Cand c;
+            c.stream = (uint32_t)s;
+            c.v = v;
+            c.miss = diff ? __ffs(diff) - 1 : -1;
+            c.pad = 0;
+            const int slot = atomicAdd(&n_stage, 1);
+            if (slot < STAGE) stage[slot] = c;
+            else {                                    // staging full: append directly
+                const unsigned int at = atomicAdd(&ctr->n_cand, 1u);
+                if (at < sp.cand_cap) cand[at] = c;
+                else atomicOr(&ctr->overflow, 1u);
+            }
+        }
+    }
+    __syncthreads();
+    block_flush(stage, min(n_stage, STAGE), cand, &ctr->n_cand, sp.cand_cap, &ctr->overflow, 1u,
+                &s_base);
+}
+
+void launch_search(const uint32_t *planes, const SearchParams &sp, Cand *cand, Counters *ctr,
+                   cudaStream_t st) {
+    const long long words = (long long)sp.n_streams * sp.tiles * PLANE_WORDS;
+    const unsigned grid = (unsigned)((words + SEARCH_THREADS - 1) / SEARCH_THREADS);
+    if (grid) k_search<<<grid, SEARCH_THREADS, 0, st>>>(planes, sp, cand, ctr);
+}
+
+// ---------------------------------------------------------------------------
+// k_precheck: one thread per candidate.  Exact fp32 matches pass; a candidate
+// with one disagreeing symbol passes only if the reference's float64 arithmetic
+// gives the sync word's bit there (i.e. the fp32 sign was the marginal one).
+// ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+k_precheck(View vw, SearchParams sp, const Cand *__restrict__ cand, Cand *__restrict__ conf,
+           Counters *ctr) {
+    const unsigned int n = min(ctr->n_cand, sp.cand_cap);
+    for (unsigned int i = blockIdx.x * blockDim.x + threadIdx.x; i < n;
+         i += gridDim.x * blockDim.x) {
+        Cand c = cand[i];
+        bool pass = c.miss < 0;
+        if (!pass) {
+            const uint32_t want = (sp.pat_rev >> c.miss) & 1u;
+            pass = exact_bit(vw, (int)c.stream, c.v + SPS * c.miss) == want;
+        }
+        if (pass) {
+            const unsigned int at = atomicAdd(&ctr->n_conf, 1u);
+            if (at < sp.conf_cap) conf[at] = c;
+            else atomicOr(&ctr->overflow, 2u);
+        }
+    }
+}
+
+void launch_precheck(const View &vw, const SearchParams &sp, const Cand *cand, Cand *conf,
+                     Counters *ctr, cudaStream_t st) {
+    k_precheck<<<148 * 4, 256, 0, st>>>(vw, sp, cand, conf, ctr);
+}
+
+// ---------------------------------------------------------------------------
+// k_confirm: one warp per surviving candidate.  All 80 symbols are decided in
+// fp64 in the reference's operation order; the first 16 must equal the sync
+// word.  Then: pack MSB-first (dsp.py:197-200), bit-reverse each byte and run
+// the table CRC over bytes 2..9 (protocol.py:290-297, crc.py:19-26), and emit
+// one record per reference call whose window holds the position at index <=
+// block_size (dsp.py:194), with that call's RSSI/SNR (dsp.py:207-236) and the
+// discriminator mean Parser.parse takes (protocol.py:304-310).
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ double warp_sum(double x) {
+#pragma unroll
+    for (int o = 16; o; o >>= 1) x += __shfl_xor_sync(0xFFFFFFFFu, x, o);
+    return x;
+}
+
+// mean |F|^2 over filtered[i0:i1) of call k, where filtered[i] = F[k*B - 1 + i]
+__device__ double mean_power(const View &vw, int s, int64_t base_g, int64_t k, int i0, int i1,
+                             int lane) {
+    double acc = 0.0;
+    for (int i = i0 + lane; i < i1; i += 32) {
+        const int64_t g = k * (int64_t)vw.block - 1 + i;
+        const Cplx f = exact_filtered(vw, s, (int)(g - base_g), g);
+        acc += f.re * f.re + f.im * f.im;
+    }
+    return warp_sum(acc) / (double)(i1 - i0);
+}
+
+constexpr int CONFIRM_WARPS = 8;
+
+__global__ void __launch_bounds__(CONFIRM_WARPS * 32)
+k_confirm(View vw, SearchParams sp, const uint32_t *__restrict__ planes,
+          const Cand *__restrict__ conf, davis_hit *__restrict__ hits, Counters *ctr,
+          int n_blocks) {
+    __shared__ uint16_t tbl[256];
+    for (int i = threadIdx.x; i < 256; i += blockDim.x) {      // crc.py:28-42, poly 0x1021
+        uint32_t reg = (uint32_t)i << 8;
+#pragma unroll
+        for (int b = 0; b < 8; b++) reg = (reg & 0x8000u) ? ((reg << 1) ^ 0x1021u) : (reg << 1);
+        tbl[i] = (uint16_t)reg;
+    }
+    __syncthreads();
+
+    const int lane = threadIdx.x & 31;
+    const unsigned int n = min(ctr->n_conf, sp.conf_cap);
+    const unsigned int warps = gridDim.x * CONFIRM_WARPS;
+    for (unsigned int ci = blockIdx.x * CONFIRM_WARPS + (threadIdx.x >> 5); ci < n; ci += warps) {
+        const Cand c = conf[ci];
+        const int s = (int)c.stream;
+        uint32_t m[3];
+        uint32_t disagree = 0;
+#pragma unroll
+        for (int part = 0; part < 3; part++) {
+            const int i = lane + 32 * part;
+            uint32_t bit = 0, fast = 0;
+            if (i < PKT_SYMS) {
+                const int v = c.v + SPS * i;
+                bit = exact_bit(vw, s, v);
+                const int sym = v / SPS, ph = v - sym * SPS;
+                fast = (planes[((size_t)s * sp.tiles_alloc + (sym >> 5)) * PLANE_WORDS + ph] >>
+                        (sym & 31)) & 1u;
+            }
+            m[part] = __ballot_sync(0xFFFFFFFFu, bit);
+            disagree |= __ballot_sync(0xFFFFFFFFu, bit != fast);
+        }
+        if ((m[0] & 0xFFFFu) != sp.pat_rev) continue;          // not a match in float64
+
+        // host-order byte b is the 8 symbols in arrival order, LSB first; the
+        // on-air (Packet.data) byte is its bit reversal.
+        uint8_t host[PKT_BYTES];
+#pragma unroll
+        for (int b = 0; b < PKT_BYTES; b++) host[b] = (uint8_t)(m[b >> 2] >> (8 * (b & 3)));
+        uint32_t reg = 0;
+#pragma unroll
+        for (int b = 2; b < PKT_BYTES; b++) reg = ((reg << 8) & 0xFFFFu) ^ tbl[(reg >> 8) ^ host[b]];
+
+        const int64_t B = vw.block, W = vw.window_blocks;
+        const int64_t done = vw.blocks_done[s];
+        const int64_t base_g = done * B - vw.n_carry;           // global index of v = 0
+        const int64_t g = base_g + c.v;
+        const int64_t k_hi = g / B + W - 1;
+        for (int64_t k = k_hi - 1; k <= k_hi; k++) {
+            const int64_t idx = g - (k - W + 1) * B;
+            if (idx < 0 || idx > B || k < done || k >= done + n_blocks) continue;
+            const int q = (int)idx;
+            const int pre = SPS * PRE_SYMS;
+            // dsp.py:207-236: filtered[] holds only the call's newest block (+1)
+            const int s1 = min(q + pre, (int)B + 1);
+            const double sig = mean_power(vw, s, base_g, k, q, s1, lane);
+            const int n0 = max(0, q - pre);
+            const double noise = q > n0 ? mean_power(vw, s, base_g, k, n0, q, lane) : 1e-9;
+            // protocol.py:304-310: discriminated[] spans blocks k-1 and k
+            double dsum = 0.0;
+            for (int t = lane; t < pre; t += 32) {
+                const int64_t gd = (k - 1) * B + q + t;
+                dsum += exact_disc(vw, s, (int)(gd - base_g));
+            }
+            dsum = warp_sum(dsum);
+            if (lane == 0) {
+                const unsigned int at = atomicAdd(&ctr->n_hit, 1u);
+                if (at < sp.hit_cap) {
+                    davis_hit h;
+                    h.position = g;
+                    h.stream = (uint32_t)(vw.stream0 + s);
+                    h.call = (uint32_t)k;
+                    h.index = q;
+#pragma unroll
+                    for (int b = 0; b < PKT_BYTES; b++)
+                        h.data[b] = (uint8_t)(__brev((uint32_t)host[b]) >> 24);
+                    h.crc_ok = reg == 0;
+                    h.flags = disagree ? 1 : 0;
+                    h.rssi = sig > 0.0 ? 10.0 * log10(sig) : -120.0;
+                    h.snr = noise > 0.0 ? 10.0 * log10(sig / noise) : 50.0;
+                    h.disc_mean = dsum / (double)pre;
+                    hits[at] = h;
+                } else {
+                    atomicOr(&ctr->overflow, 4u);
+                }
+            }
+        }
+    }
+}
+
+void launch_confirm(const View &vw, const SearchParams &sp, const uint32_t *planes,
+                    const Cand *conf, davis_hit *hits, Counters *ctr, int n_blocks,
+                    cudaStream_t st) {
+    k_confirm<<<148 * 2, CONFIRM_WARPS * 32, 0, st>>>(vw, sp, planes, conf, hits, ctr, n_blocks);
+}
+
+// ---------------------------------------------------------------------------
+// k_carry: keep the last `keep` samples of (old carry || input) per stream and
+// advance the per-stream call counter.  Ping-pong buffers: old and new differ.
+// ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+k_carry(const uint8_t *__restrict__ carry_old, uint8_t *__restrict__ carry_new,
+        size_t carry_stride, int keep, const uint8_t *__restrict__ input, size_t input_stride,
+        int n_new, int64_t *blocks_done, int n_blocks) {
+    const int s = blockIdx.y;
+    const long long keep_b = 2LL * keep, new_b = 2LL * n_new;
+    const long long chunks = keep_b / 16;
+    for (long long c = (long long)blockIdx.x * blockDim.x + threadIdx.x; c < chunks;
+         c += (long long)gridDim.x * blockDim.x) {
+        // byte c*16 of the new carry = byte (c*16 + new_b) of (old carry || input)
+        const long long off = 16 * c + new_b;
+        const uint8_t *src = off < keep_b ? carry_old + (size_t)s * carry_stride + off
+                                          : input + (size_t)s * input_stride + (off - keep_b);
+        *reinterpret_cast<uint4 *>(carry_new + (size_t)s * carry_stride + 16 * c) =
+            *reinterpret_cast<const uint4 *>(src);
+    }
+    if (blockIdx.x == 0 && threadIdx.x == 0) blocks_done[s] += n_blocks;
+}
+
+void launch_carry(const uint8_t *carry_old, uint8_t *carry_new, size_t carry_stride, int keep,
+                  const uint8_t *input, size_t input_stride, int n_new, int n_streams,
+                  int64_t *blocks_done, int n_blocks, cudaStream_t st) {
+    const long long chunks = 2LL * keep / 16;
+    int gx = (int)min((chunks + 255) / 256, 8LL);
+    for (int s0 = 0; s0 < n_streams; s0 += 65535) {
+        const int ns = min(65535, n_streams - s0);
+        k_carry<<<dim3(gx, ns), 256, 0, st>>>(
+            carry_old + (size_t)s0 * carry_stride, carry_new + (size_t)s0 * carry_stride,
+            carry_stride, keep, input + (size_t)s0 * input_stride, input_stride, n_new,
+            blocks_done + s0, n_blocks);
+    }
+}
+
+// ---------------------------------------------------------------------------
+// debug / parity taps
+// ---------------------------------------------------------------------------
+__global__ void k_exact_disc(View vw, int stream, int v0, int n, double *out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = exact_disc(vw, stream, v0 + i);
+}
+
+void launch_exact_disc(const View &vw, int stream, int v0, int n, double *out, cudaStream_t st) {
+    if (n > 0) k_exact_disc<<<(n + 255) / 256, 256, 0, st>>>(vw, stream, v0, n, out);
+}
+
+// CRC.checksum for arbitrary (init, poly) with a shared-memory table built as
+// crc.py:28-42 builds it; one thread per byte string.
+__global__ void k_crc16(const uint8_t *__restrict__ data, size_t n, size_t len, uint16_t init,
+                        uint16_t poly, int swap_bits, uint16_t *__restrict__ out) {
+    __shared__ uint16_t tbl[256];
+    for (int i = threadIdx.x; i < 256; i += blockDim.x) {
+        uint32_t reg = (uint32_t)i << 8;
+        for (int b = 0; b < 8; b++) reg = (reg & 0x8000u) ? ((reg << 1) ^ poly) : (reg << 1);
+        tbl[i] = (uint16_t)reg;
+    }
+    __syncthreads();
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    uint32_t reg = init;
+    for (size_t b = 0; b < len; b++) {
+        uint32_t byte = data[i * len + b];
+        if (swap_bits) byte = __brev(byte) >> 24;
+        reg = ((reg << 8) & 0xFFFFu) ^ tbl[((reg >> 8) ^ byte) & 0xFFu];
+    }
+    out[i] = (uint16_t)reg;
+}
+
+void launch_crc16(const uint8_t *data, size_t n, size_t len, uint16_t init, uint16_t poly,
+                  int swap_bits, uint16_t *out, cudaStream_t st) {
+    if (n) k_crc16<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(data, n, len, init, poly,
+                                                                 swap_bits, out);
+}
+
+}  // namespace davis

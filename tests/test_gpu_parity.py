@@ -1,0 +1,314 @@
+"""GPU parity: the CUDA path (through the C ABI) against the oracle and the
+reference-generated golden fixtures.  Integer/byte/index results are compared
+bit-exactly; floating-point taps use the tolerances written in each test."""
+import numpy as np
+import pytest
+
+from conftest import golden_rows, load_golden
+from oracle import c_oracle as CO
+from oracle import davis_oracle as O
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def dsp():
+    from rtldavis_b200 import dsp as d
+    return d
+
+
+@pytest.fixture(scope="module")
+def protocol():
+    from rtldavis_b200 import protocol as p
+    return p
+
+
+def _cfg(dsp, block):
+    return dsp.PacketConfig(19200, 14, 16, 80, "1100101110001001", block_size=block)
+
+
+def _rows(hits, first_call=0):
+    return [(int(h["call"]) - first_call, int(h["index"]), h["data"].tobytes(), bool(h["crc_ok"]))
+            for h in hits]
+
+
+# ---------------------------------------------------------------------------
+# golden fixtures (outputs of the unmodified reference)
+# ---------------------------------------------------------------------------
+@pytest.mark.parametrize("name", ["hi_snr_8192", "lo_snr_8192", "go_block_512"])
+def test_single_stream_drop_in_matches_reference(dsp, name):
+    g = load_golden(name)
+    B = int(g["block"])
+    dem = dsp.Demodulator(_cfg(dsp, B))
+    iq = g["iq"]
+    got, rssi, snr = [], [], []
+    for k in range(iq.size // (2 * B)):
+        pk = dem.demodulate(iq[2 * B * k:2 * B * (k + 1)])
+        for p, h in zip(pk, dem.last_hits):
+            got.append((k, p.index, p.data.tobytes(), bool(h["crc_ok"])))
+            rssi.append(p.rssi)
+            snr.append(p.snr)
+    assert got == golden_rows(g)
+    # fp64 on both sides, different summation order: 1e-9 dB absolute
+    np.testing.assert_allclose(rssi, g["pk_rssi"], rtol=0, atol=1e-9)
+    np.testing.assert_allclose(snr, g["pk_snr"], rtol=0, atol=1e-9)
+    dem.close()
+
+
+@pytest.mark.parametrize("name", ["hi_snr_8192", "lo_snr_8192", "go_block_512"])
+@pytest.mark.parametrize("chunks", ["all", "odd"])
+def test_batched_blocks_match_reference(dsp, name, chunks):
+    """Many blocks per call, and ragged multi-block chunks (carried state)."""
+    g = load_golden(name)
+    B = int(g["block"])
+    iq = g["iq"]
+    n = iq.size // (2 * B)
+    sizes = [n] if chunks == "all" else []
+    if chunks == "odd":
+        left, step = n, 1
+        while left:
+            take = min(left, step)
+            sizes.append(take)
+            left -= take
+            step = step % 5 + 2
+    bd = dsp.BatchDemodulator(_cfg(dsp, B), 1, max_blocks=max(sizes))
+    got, at = [], 0
+    for take in sizes:
+        bd.submit(iq[2 * B * at:2 * B * (at + take)].reshape(1, -1))
+        got += _rows(bd.fetch())
+        at += take
+    assert got == golden_rows(g)
+    bd.close()
+
+
+def test_discriminated_attribute_matches_reference(dsp):
+    """Demodulator.discriminated (dsp.py:133,162), float64, against the fixture
+    slice and the oracle; 1e-12 relative (summation order only)."""
+    g = load_golden("hi_snr_8192")
+    B = int(g["block"])
+    dem = dsp.Demodulator(_cfg(dsp, B))
+    iq = g["iq"]
+    lo, hi = int(g["disc_lo"]), int(g["disc_hi"])
+    k_end = hi // B + 1
+    for k in range(k_end):
+        dem.demodulate(iq[2 * B * k:2 * B * (k + 1)])
+    d = dem.discriminated                       # global samples [(k_end-2)B, k_end*B)
+    first = (k_end - 2) * B
+    a, b = max(lo, first), min(hi, k_end * B)
+    ref = g["disc"][a - lo:b - lo]
+    got = d[a - first:b - first]
+    assert np.all(np.abs(got - ref) <= 1e-12 * np.maximum(np.abs(ref), 1.0))
+    full = O.stream_discriminated(iq[: 2 * B * k_end])[first:]
+    assert np.all(np.abs(d - full) <= 1e-12 * np.maximum(np.abs(full), 1.0))
+    dem.close()
+
+
+def test_first_call_zero_history(dsp):
+    """After construction `discriminated` is zero for the older block and the
+    very first samples follow the signed-zero rule."""
+    B = 8192
+    iq = np.full(2 * B, 128, dtype=np.uint8)
+    iq[0], iq[1] = 10, 200
+    dem = dsp.Demodulator(_cfg(dsp, B))
+    assert dem.demodulate(iq) == []
+    d = dem.discriminated
+    assert not d[:B].any()
+    ref = O.stream_discriminated(iq)
+    assert np.array_equal(np.signbit(d[B:B + 16]), np.signbit(ref[:16]))
+    assert np.signbit(d[B + 1])                  # -0.0 / tiny negative: bit 63 set
+    dem.close()
+
+
+# ---------------------------------------------------------------------------
+# seeded synthetic batches against the C oracle
+# ---------------------------------------------------------------------------
+def _batch(n_streams, n_blocks, snr, **kw):
+    from rtldavis_b200 import synth
+    iq, truth = synth.make_batch(n_streams, n_blocks * 8192, kw.pop("n_packets", 3), snr, **kw)
+    return iq, truth
+
+
+def _oracle_rows(iq, block=8192):
+    rec = CO.batch_records(iq, block=block)
+    return [(int(r["stream"]), int(r["call"]), int(r["index"]), r["data"].tobytes(),
+             bool(r["crc_ok"])) for r in rec]
+
+
+def _gpu_rows(hits):
+    return [(int(h["stream"]), int(h["call"]), int(h["index"]), h["data"].tobytes(),
+             bool(h["crc_ok"])) for h in hits]
+
+
+@pytest.mark.parametrize("snr", [30.0, 10.0, 4.0])
+def test_batch_of_streams_matches_oracle(dsp, protocol, snr):
+    iq, truth = _batch(12, 16, snr, seed0=100, df_range_hz=3000.0, ppm_range=50.0)
+    bd = dsp.BatchDemodulator(protocol.new_packet_config(14), 12, max_blocks=16)
+    bd.submit(iq)
+    hits = bd.fetch()
+    assert _gpu_rows(hits) == _oracle_rows(iq)
+    if snr >= 30:
+        valid = {(int(h["stream"]), bytes(protocol.swap_bit_order(b) for b in h["data"][2:]))
+                 for h in hits if h["crc_ok"]}
+        for s, pk in enumerate(truth):
+            for e in pk:
+                assert (s, e.message) in valid
+    bd.close()
+
+
+def test_device_resident_input_equals_host_input(dsp, protocol):
+    import torch
+    iq, _ = _batch(6, 8, 20.0, seed0=300)
+    cfg = protocol.new_packet_config(14)
+    a = dsp.BatchDemodulator(cfg, 6, max_blocks=8)
+    a.submit(iq)
+    host = a.fetch()
+    b = dsp.BatchDemodulator(cfg, 6, max_blocks=8)
+    dev = torch.from_numpy(iq).cuda()
+    b.submit(dev)
+    devh = b.fetch()
+    assert _gpu_rows(host) == _gpu_rows(devh) == _oracle_rows(iq)
+    a.close()
+    b.close()
+
+
+def test_host_pipeline_groups(dsp, protocol):
+    """Host input split over several pipeline stages and groups."""
+    iq, _ = _batch(10, 6, 25.0, seed0=400)
+    bd = dsp.BatchDemodulator(protocol.new_packet_config(14), 10, max_blocks=6, host_slots=2,
+                              host_group=3)
+    bd.submit(iq)
+    assert _gpu_rows(bd.fetch()) == _oracle_rows(iq)
+    bd.close()
+
+
+def test_decision_bits_and_fp32_discriminator(dsp, protocol):
+    """Gate (ii)/(iii) of SURVEY 8(d): fp32 decision bits equal the float64 ones
+    except where the discriminator is within 1e-5 of zero relative to its scale
+    (counted), and the fp32 discriminator is within 1e-5 relative with a floor."""
+    from rtldavis_b200 import synth
+    n_blocks = 24
+    cap = synth.make_capture(77, n_blocks * 8192, 6, snr_db=12.0, df_hz=1000.0)
+    bd = dsp.BatchDemodulator(protocol.new_packet_config(14), 1, max_blocks=n_blocks)
+    bd.submit(cap.iq.reshape(1, -1))
+    bd.fetch()
+    first, bits = bd.debug_bits(0)
+    ref_bits, ref_disc = CO.stream_bits(cap.iq, want_disc=True)
+    lo = max(first, 16)
+    got = bits[lo - first:lo - first + ref_bits.size - lo]
+    want = ref_bits[lo:lo + got.size]
+    bad = np.flatnonzero(got != want)
+    # every disagreement must sit where |D| is negligible
+    assert np.all(np.abs(ref_disc[lo + bad]) < 1e-5)
+    assert bad.size <= 1e-5 * want.size + 2, f"{bad.size} fp32 sign disagreements"
+    d32 = bd.discriminated_fp32(0).astype(np.float64)
+    tail = ref_disc[-2 * 8192:]
+    tol = 1e-5 * np.maximum(np.abs(tail), 1.0)
+    n_out = int(np.sum(np.abs(d32 - tail) > tol))
+    assert n_out <= 1e-3 * tail.size, f"{n_out} fp32 discriminator samples outside 1e-5"
+    bd.close()
+
+
+def test_reset_restarts_the_stream(dsp, protocol):
+    iq, _ = _batch(2, 6, 30.0, seed0=500)
+    bd = dsp.BatchDemodulator(protocol.new_packet_config(14), 2, max_blocks=6)
+    bd.submit(iq)
+    first = _gpu_rows(bd.fetch())
+    bd.reset()
+    bd.submit(iq)
+    again = _gpu_rows(bd.fetch())
+    assert first == again == _oracle_rows(iq)
+    bd.close()
+
+
+def test_wrong_sizes_raise_like_the_reference(dsp, protocol):
+    dem = dsp.Demodulator(protocol.new_packet_config(14))
+    with pytest.raises(ValueError, match="Incompatible array sizes"):
+        dem.demodulate(np.zeros(100, dtype=np.uint8))
+    bd = dsp.BatchDemodulator(protocol.new_packet_config(14), 2, max_blocks=2)
+    with pytest.raises(ValueError):
+        bd.submit(np.zeros((2, 3 * 16384), dtype=np.uint8))     # more blocks than max_blocks
+    with pytest.raises(ValueError):
+        bd.submit(np.zeros((3, 16384), dtype=np.uint8))         # wrong stream count
+    with pytest.raises(ValueError):
+        dsp.BatchDemodulator(dsp.PacketConfig(19200, 10, 16, 80, "1100101110001001", 8192))
+    dem.close()
+    bd.close()
+
+
+def test_noise_only_has_no_valid_packets(dsp, protocol):
+    from rtldavis_b200 import synth
+    cap = synth.make_capture(9, 64 * 8192, 0, noise_only=True)
+    bd = dsp.BatchDemodulator(protocol.new_packet_config(14), 1, max_blocks=64)
+    bd.submit(cap.iq.reshape(1, -1))
+    hits = bd.fetch()
+    assert _gpu_rows(hits) == _oracle_rows(cap.iq.reshape(1, -1))
+    assert not hits["crc_ok"].any()
+    bd.close()
+
+
+# ---------------------------------------------------------------------------
+# CRC kernel against the reference's vectors
+# ---------------------------------------------------------------------------
+def test_crc_kernel_kats(protocol):
+    from rtldavis_b200.crc import CRC
+    crc = CRC("CCITT-16", 0, 0x1021, 0)
+    air = bytes([0x07, 0xC0, 0x2B, 0x0B, 0x80, 0x40, 0x8E, 0xFF])       # tests/test_protocol.py:29
+    swapped = bytes(protocol.swap_bit_order(b) for b in air)
+    assert int(crc.checksum(swapped)) == 0
+    assert int(crc.checksum(swapped[:-1] + b"\x7e")) != 0
+    for frame in ["80052c2cf90b649e", "a006528338005ac8", "a00435d12b00703a", "81058D33CB0FF1DD"]:
+        assert int(crc.checksum(bytes.fromhex(frame))) == 0
+    # on-device bit swap + CRC in one launch
+    rows = np.frombuffer(air, dtype=np.uint8).reshape(1, -1)
+    assert int(crc.checksum_many(rows, swap_bits=True)[0]) == 0
+
+
+@pytest.mark.parametrize("init,poly", [(0, 0x8005), (0, 0x6F63), (0xFFFF, 0x1021), (0, 0x1021)])
+def test_crc_kernel_identity_and_oracle(init, poly):
+    """crc/crc_test.go:22-41 on the device, plus equality with the oracle."""
+    from rtldavis_b200.crc import CRC
+    rng = np.random.default_rng(poly + init)
+    crc = CRC("x", init, poly, 0)
+    tbl = O.crc_table(poly)
+    for n in (8, 10, 16, 38):
+        body = rng.integers(0, 256, (512, n - 2), dtype=np.uint8)
+        c = crc.checksum_many(body)
+        assert [int(x) for x in c[:32]] == [O.crc16(r.tolist(), init, tbl) for r in body[:32]]
+        whole = np.concatenate([body, (c >> 8).astype(np.uint8)[:, None],
+                                (c & 0xFF).astype(np.uint8)[:, None]], axis=1)
+        assert not crc.checksum_many(whole).any()
+
+
+# ---------------------------------------------------------------------------
+# device-side generator + full-size style property
+# ---------------------------------------------------------------------------
+def test_device_generator_round_trip(dsp, protocol):
+    """encode -> channel -> decode: every packet the generator embedded comes
+    back CRC-valid with the same message, and the result equals the oracle's on
+    a copy of the same bytes."""
+    import ctypes as C
+
+    import torch
+    from rtldavis_b200 import _lib
+    L = _lib.load()
+    n_streams, n_blocks, n_packets = 16, 40, 5
+    n_samples = n_blocks * 8192
+    buf = torch.empty((n_streams, 2 * n_samples), dtype=torch.uint8, device="cuda")
+    _lib.check(L.davis_synth_fill(buf.data_ptr(), n_streams, 2 * n_samples, n_samples, 1234,
+                                  n_packets, 20.0, 2500.0, 50.0, 0, None))
+    torch.cuda.synchronize()
+    msgs = np.zeros((n_streams, n_packets, 8), dtype=np.uint8)
+    starts = np.zeros((n_streams, n_packets), dtype=np.int64)
+    _lib.check(L.davis_synth_truth(n_streams, n_samples, 1234, n_packets, 20.0,
+                                   msgs.ctypes.data, starts.ctypes.data))
+    bd = dsp.BatchDemodulator(protocol.new_packet_config(14), n_streams, max_blocks=n_blocks)
+    bd.submit(buf)
+    hits = bd.fetch()
+    host = buf.cpu().numpy()
+    assert _gpu_rows(hits) == _oracle_rows(host)
+    valid = {(int(h["stream"]), bytes(protocol.swap_bit_order(b) for b in h["data"][2:]))
+             for h in hits if h["crc_ok"]}
+    missing = [(s, k) for s in range(n_streams) for k in range(n_packets)
+               if (s, msgs[s, k].tobytes()) not in valid]
+    assert not missing, f"embedded packets not recovered: {missing}"
+    bd.close()
