@@ -24,6 +24,9 @@ struct Stage {
     uint32_t *planes = nullptr;  size_t planes_words = 0;
     Cand *cand = nullptr;        unsigned int cand_cap = 0;
     Cand *conf = nullptr;        unsigned int conf_cap = 0;
+    Rec *recs = nullptr;         size_t recs_cap = 0;
+    uint32_t *tbl = nullptr;     size_t tbl_size = 0;        // dedupe table, power of two
+    uint8_t *lost = nullptr;     size_t lost_cap = 0;
     Counters *ctr = nullptr;
     int last_group = -1;
     int tiles_alloc = 0;
@@ -45,6 +48,7 @@ struct davis_handle {
     uint8_t *carry[2] = {nullptr, nullptr};
     int cur = 0;
     int64_t *d_blocks_done = nullptr;
+    double *d_lut = nullptr;                          // dsp.py:26 table, float64
     std::vector<int64_t> h_blocks_done;
     uint32_t pat_rev = 0;
 
@@ -90,7 +94,8 @@ int grow(davis_handle *h, T **p, size_t *have, size_t want) {
 
 int tiles_needed(int v_len) { return (v_len + TILE - 1) / TILE; }
 
-int prepare_stage(davis_handle *h, Stage &st, int ns, int n_blocks, size_t staging_bytes) {
+int prepare_stage(davis_handle *h, Stage &st, int ns, int n_blocks, size_t staging_bytes,
+                  size_t rec_cap) {
     const int v_len = h->n_carry + n_blocks * h->B;
     int tiles = tiles_needed(v_len) + 1;                       // +1: the search reads tile j+1
     tiles = (tiles + DEMOD_WARPS - 1) / DEMOD_WARPS * DEMOD_WARPS;
@@ -107,6 +112,15 @@ int prepare_stage(davis_handle *h, Stage &st, int ns, int n_blocks, size_t stagi
     have = st.conf_cap;
     if ((rc = grow(h, &st.conf, &have, want / 2))) return rc;
     st.conf_cap = (unsigned int)have;
+    if ((rc = grow(h, &st.recs, &st.recs_cap, rec_cap))) return rc;
+    if ((rc = grow(h, &st.lost, &st.lost_cap, rec_cap))) return rc;
+    size_t tbl = 1024;
+    while (tbl < 2 * rec_cap) tbl <<= 1;                       // load factor <= 0.5
+    if (st.tbl_size < tbl) {
+        size_t have_t = st.tbl_size;
+        if ((rc = grow(h, &st.tbl, &have_t, tbl))) return rc;
+        st.tbl_size = tbl;
+    }
     if (!st.ctr) CU(cudaMalloc((void **)&st.ctr, sizeof(Counters)));
     if (!st.st) CU(cudaStreamCreateWithFlags(&st.st, cudaStreamNonBlocking));
     return DAVIS_OK;
@@ -143,6 +157,7 @@ int run_group(davis_handle *h, Stage &stage, Group &g, int gi, const uint8_t *de
     vw.block = h->B;
     vw.window_blocks = h->W;
     vw.stream0 = g.s0;
+    vw.lut = h->d_lut;
 
     SearchParams sp;
     sp.pat_rev = h->pat_rev;
@@ -154,15 +169,20 @@ int run_group(davis_handle *h, Stage &stage, Group &g, int gi, const uint8_t *de
     sp.cand_cap = stage.cand_cap;
     sp.conf_cap = stage.conf_cap;
     sp.hit_cap = g.hit_cap;
+    sp.tbl_mask = (unsigned int)(stage.tbl_size - 1);
 
     CU(cudaMemsetAsync(stage.ctr, 0, sizeof(Counters), st));
+    CU(cudaMemsetAsync(stage.tbl, 0xFF, stage.tbl_size * sizeof(uint32_t), st));
+    CU(cudaMemsetAsync(stage.lost, 0, g.hit_cap, st));
     CU(cudaEventRecord(g.ev[0], st));
     launch_demod(vw, stage.planes, g.ns, stage.tiles_alloc, h->variant, nullptr, 0, st);
     CU(cudaEventRecord(g.ev[1], st));
     launch_search(stage.planes, sp, stage.cand, stage.ctr, st);
     CU(cudaEventRecord(g.ev[2], st));
     launch_precheck(vw, sp, stage.cand, stage.conf, stage.ctr, st);
-    launch_confirm(vw, sp, stage.planes, stage.conf, h->d_hits + g.hit_off, stage.ctr, n_blocks, st);
+    launch_confirm(vw, sp, stage.planes, stage.conf, stage.recs, stage.tbl, stage.lost, stage.ctr,
+                   n_blocks, st);
+    launch_finalize(vw, sp, stage.recs, stage.lost, h->d_hits + g.hit_off, stage.ctr, st);
     launch_carry(h->carry[h->cur] + (size_t)g.s0 * h->carry_stride,
                  h->carry[h->cur ^ 1] + (size_t)g.s0 * h->carry_stride, h->carry_stride, h->n_keep,
                  dev_input, input_stride, n_blocks * h->B, g.ns, h->d_blocks_done + g.s0, n_blocks,
@@ -172,7 +192,7 @@ int run_group(davis_handle *h, Stage &stage, Group &g, int gi, const uint8_t *de
     CU(cudaEventRecord(g.ev[4], st));
     CU(cudaGetLastError());
     stage.last_group = gi;
-    h->stats.launches += 4 + (uint64_t)((g.ns + 65534) / 65535);
+    h->stats.launches += 5 + (uint64_t)((g.ns + 65534) / 65535);
     return DAVIS_OK;
 }
 
@@ -241,6 +261,13 @@ int davis_create(const davis_cfg *cfg, int n_streams, int device, davis_handle *
     if (cudaMalloc((void **)&h->d_blocks_done, sizeof(int64_t) * n_streams) != cudaSuccess)
         return bail(DAVIS_E_NOMEM);
     cudaMemset(h->d_blocks_done, 0, sizeof(int64_t) * n_streams);
+    {
+        double lut[256];                                         // dsp.py:26, same float64 ops
+        for (int i = 0; i < 256; i++) lut[i] = ((double)i - 127.4) / 127.6;
+        if (cudaMalloc((void **)&h->d_lut, sizeof lut) != cudaSuccess) return bail(DAVIS_E_NOMEM);
+        if (cudaMemcpy(h->d_lut, lut, sizeof lut, cudaMemcpyHostToDevice) != cudaSuccess)
+            return bail(DAVIS_E_CUDA);
+    }
     int slots = cfg->host_slots > 0 ? cfg->host_slots : 3;
     h->stages.resize(slots);
     if (cudaDeviceSynchronize() != cudaSuccess) return bail(DAVIS_E_CUDA);
@@ -259,11 +286,15 @@ int davis_destroy(davis_handle *h) {
         if (s.planes) cudaFree(s.planes);
         if (s.cand) cudaFree(s.cand);
         if (s.conf) cudaFree(s.conf);
+        if (s.recs) cudaFree(s.recs);
+        if (s.tbl) cudaFree(s.tbl);
+        if (s.lost) cudaFree(s.lost);
         if (s.ctr) cudaFree(s.ctr);
         if (s.st) cudaStreamDestroy(s.st);
     }
     for (int i = 0; i < 2; i++) if (h->carry[i]) cudaFree(h->carry[i]);
     if (h->d_blocks_done) cudaFree(h->d_blocks_done);
+    if (h->d_lut) cudaFree(h->d_lut);
     if (h->d_hits) cudaFree(h->d_hits);
     if (h->h_ctr) cudaFreeHost(h->h_ctr);
     delete h;
@@ -332,7 +363,7 @@ int davis_demod_u8(davis_handle *h, const uint8_t *iq, size_t bytes_per_stream,
         g.s0 = gi * per_group;
         g.ns = std::min(per_group, h->n_streams - g.s0);
         size_t cap = h->cfg.max_hits > 0 ? (size_t)h->cfg.max_hits
-                                         : 1024 + (size_t)g.ns * ((size_t)n_blocks + h->W) * 4;
+                                         : 4096 + (size_t)g.ns * ((size_t)n_blocks + h->W) * 6;
         g.hit_cap = (unsigned int)std::min<size_t>(cap, 0x7FFFFFFFu);
         g.hit_off = hit_total;
         hit_total += g.hit_cap;
@@ -351,7 +382,8 @@ int davis_demod_u8(davis_handle *h, const uint8_t *iq, size_t bytes_per_stream,
         Group &g = h->groups[gi];
         Stage &stage = h->stages[g.stage];
         const size_t stage_bytes = on_device ? 0 : (size_t)per_group * bytes_per_stream;
-        if ((rc = prepare_stage(h, stage, on_device ? h->n_streams : per_group, n_blocks, stage_bytes)))
+        if ((rc = prepare_stage(h, stage, on_device ? h->n_streams : per_group, n_blocks, stage_bytes,
+                                g.hit_cap)))
             return rc;
         cudaStream_t st = stage.st;
         const uint8_t *dev_in;
@@ -396,13 +428,13 @@ int davis_fetch_hits(davis_handle *h, davis_hit *out, size_t cap, size_t *n) {
             CU(cudaEventElapsedTime(&ms, g.ev[2], g.ev[3])); finish += ms;
             h->stats.candidates += c.n_cand;
             h->stats.confirmed += c.n_conf;
-            h->stats.records += c.n_hit;
+            h->stats.records += c.n_rec;
             if (c.overflow) {
                 h->queued = false;
                 char msg[160];
                 snprintf(msg, sizeof msg,
-                         "device buffer overflow (mask %u): cand %u conf %u hits %u; raise max_hits",
-                         c.overflow, c.n_cand, c.n_conf, c.n_hit);
+                         "device buffer overflow (mask %u): cand %u conf %u records %u; raise max_hits",
+                         c.overflow, c.n_cand, c.n_conf, c.n_rec);
                 return fail(h, DAVIS_E_OVERFLOW, msg);
             }
             const size_t at = h->results.size();
@@ -427,20 +459,21 @@ int davis_fetch_hits(davis_handle *h, davis_hit *out, size_t cap, size_t *n) {
             }
             h->stats.total_ms = first_to_last;
         }
-        // reference order + per-call dedupe on the payload (dsp.py:203-205)
-        std::sort(h->results.begin(), h->results.end(), hit_less);
-        size_t w = 0, call_begin = 0;
-        for (size_t i = 0; i < h->results.size(); i++) {
-            const davis_hit &r = h->results[i];
-            if (w == 0 || h->results[call_begin].stream != r.stream ||
-                h->results[call_begin].call != r.call)
-                call_begin = w;
-            bool dup = false;
-            for (size_t j = call_begin; j < w && !dup; j++)
-                dup = !memcmp(h->results[j].data, r.data, PKT_BYTES);
-            if (!dup) h->results[w++] = r;
+        // The device already applied the per-call dedupe (dsp.py:203-205); what is
+        // left is the reference's order: stream, call, then (index mod 14, index)
+        // (dsp.py:175-186).  Bucket by stream, then sort the short buckets.
+        {
+            const size_t n_res = h->results.size();
+            std::vector<uint32_t> start((size_t)h->n_streams + 1, 0);
+            for (const davis_hit &r : h->results) start[r.stream + 1]++;
+            for (int s = 0; s < h->n_streams; s++) start[s + 1] += start[s];
+            std::vector<davis_hit> sorted(n_res);
+            std::vector<uint32_t> fill(start.begin(), start.end() - 1);
+            for (const davis_hit &r : h->results) sorted[fill[r.stream]++] = r;
+            for (int s = 0; s < h->n_streams; s++)
+                std::sort(sorted.begin() + start[s], sorted.begin() + start[s + 1], hit_less);
+            h->results.swap(sorted);
         }
-        h->results.resize(w);
         h->queued = false;
         h->have_results = true;
     } else if (!h->have_results) {
@@ -499,6 +532,7 @@ static int debug_view(davis_handle *h, View *vw) {
     vw->block = h->B;
     vw->window_blocks = h->W;
     vw->stream0 = 0;
+    vw->lut = h->d_lut;
     return DAVIS_OK;
 }
 

@@ -17,13 +17,15 @@
 //
 // Arithmetic (fp32, signs only)
 //   x = (u - 127.4)/127.6 and the division by |F|^2 + eps are positive scalings
-//   and are dropped; the -127.4 offset survives the filter as a period-4
-//   constant (127.4 * (2c0 - 2c2 + c4) * (1+j) * j^q) folded into the first FMA;
+//   and are dropped; bytes are centred exactly (u - 127) while unpacking and the
+//   remaining -0.4 of the LUT offset survives the filter as a period-4 constant
+//   (0.4 * (2c0 - 2c2 + c4) * (1+j) * j^q) folded into the first FMA;
 //   the rotation j^i is applied while unpacking bytes (which byte lands in which
 //   component, and with which sign, is a PRMT selector); the rotation phase is
 //   taken relative to the lane's window because a common unit factor cancels in
 //   Im(conj(F[n-1]) F[n]).  Bytes become floats without I2F: PRMT builds the
-//   bit pattern of +-(2^23 + u) and one packed add of -+2^23 leaves +-u exactly.
+//   bit pattern of +-(2^23 + u) and one packed add of -+(2^23 + 127) leaves
+//   +-(u - 127) exactly.
 //   Every decision that reaches a caller is re-derived in fp64 by the confirm
 //   kernel, so an fp32 sign that disagrees with the reference's float64 (only
 //   possible when the cross product is ~1e-7 of |F|^2) cannot change a packet.
@@ -61,7 +63,7 @@ __device__ __forceinline__ float2 unpack_rotated(uint32_t w) {
     constexpr uint32_t sel_im = src_im | 0x440u | ((neg_im ? 6u : 5u) << 12);
     float2 raw = f2(__uint_as_float(__byte_perm(w, POOL, sel_re)),
                     __uint_as_float(__byte_perm(w, POOL, sel_im)));
-    constexpr float M = 8388608.0f;
+    constexpr float M = 8388608.0f + 127.0f;   // leaves +-(u - 127): keeps the FIR free of the DC pedestal
     return cadd<PACKED>(raw, f2(neg_re ? M : -M, neg_im ? M : -M));
 }
 
@@ -115,12 +117,12 @@ k_demod(View vw, uint32_t *__restrict__ planes, int tiles_alloc, int groups,
 
     const float c0 = (float)DAVIS_C0, c1 = (float)DAVIS_C1, c2 = (float)DAVIS_C2,
                 c3 = (float)DAVIS_C3, c4 = (float)DAVIS_C4;
-    const float K = (float)(127.4 * (2.0 * DAVIS_C0 - 2.0 * DAVIS_C2 + DAVIS_C4));
+    const float K = (float)(0.4 * (2.0 * DAVIS_C0 - 2.0 * DAVIS_C2 + DAVIS_C4));
 
     float2 F[15];
 #pragma unroll
     for (int q = 0; q < 15; q++) {
-        // -127.4 * S * (1+j) * j^q
+        // -0.4 * S * (1+j) * j^q  (samples are u - 127, the LUT subtracts 127.4)
         const float2 off = (q & 3) == 0 ? f2(-K, -K) : (q & 3) == 1 ? f2(K, -K)
                          : (q & 3) == 2 ? f2(K, K) : f2(-K, K);
         float2 acc = cfma<PACKED>(f2(c4, c4), r[q + 4], off);

@@ -44,7 +44,14 @@ struct View {
     int block;                // block_size
     int window_blocks;        // W = buffer_length / block_size
     int stream0;              // first stream of this pipeline stage (for records)
+    const double *lut;        // device copy of the float64 byte->sample table (256 entries)
 };
+
+// copy the table into shared memory (call from every thread of the block)
+__device__ __forceinline__ void stage_lut(double *sm_lut, const double *lut) {
+    for (int i = threadIdx.x; i < 256; i += blockDim.x) sm_lut[i] = lut[i];
+    __syncthreads();
+}
 
 __device__ __forceinline__ const uint8_t *sample_ptr(const View &vw, int s, int v) {
     return v < vw.n_carry ? vw.carry + (size_t)s * vw.carry_stride + 2 * (size_t)v
@@ -61,12 +68,17 @@ __device__ __forceinline__ int64_t global_of(const View &vw, int s, int v) {
 struct Cplx { double re, im; };
 
 // rotated sample r[g] = lut(u) * j^(g mod 4); zero before the stream began
-__device__ __forceinline__ Cplx exact_rotated(const View &vw, int s, int v, int64_t g) {
+// `lut` is the reference's 256-entry table (u - 127.4) / 127.6 (dsp.py:26), built
+// once on the host in float64 and staged in shared memory by every kernel that
+// evaluates the exact form (a divide per sample would dominate those kernels).
+__device__ __forceinline__ Cplx exact_rotated(const double *lut, const View &vw, int s, int v,
+                                              int64_t g) {
     Cplx r{0.0, 0.0};
     if (g < 0 || v < 0) return r;
     const uint8_t *p = sample_ptr(vw, s, v);
-    double xr = __ddiv_rn(__dsub_rn((double)p[0], 127.4), 127.6);
-    double xi = __ddiv_rn(__dsub_rn((double)p[1], 127.4), 127.6);
+    const uchar2 u = *reinterpret_cast<const uchar2 *>(p);
+    double xr = lut[u.x];
+    double xi = lut[u.y];
     switch ((int)(g & 3)) {
     case 0: r.re = xr;  r.im = xi;  break;
     case 1: r.re = -xi; r.im = xr;  break;
@@ -77,13 +89,14 @@ __device__ __forceinline__ Cplx exact_rotated(const View &vw, int s, int v, int6
 }
 
 // F[g] = sum_m taps[m] * r[g-9+m], summed m = 0..8
-__device__ __forceinline__ Cplx exact_filtered(const View &vw, int s, int v, int64_t g) {
+__device__ __forceinline__ Cplx exact_filtered(const double *lut, const View &vw, int s, int v,
+                                               int64_t g) {
     const double taps[9] = {DAVIS_C0, DAVIS_C1, DAVIS_C2, DAVIS_C3, DAVIS_C4,
                             DAVIS_C3, DAVIS_C2, DAVIS_C1, DAVIS_C0};
     Cplx f{0.0, 0.0};
 #pragma unroll
     for (int m = 0; m < 9; m++) {
-        Cplx r = exact_rotated(vw, s, v - 9 + m, g - 9 + m);
+        Cplx r = exact_rotated(lut, vw, s, v - 9 + m, g - 9 + m);
         f.re = __dadd_rn(f.re, __dmul_rn(taps[m], r.re));
         f.im = __dadd_rn(f.im, __dmul_rn(taps[m], r.im));
     }
@@ -97,17 +110,17 @@ __device__ __forceinline__ double exact_disc_from(const Cplx &a, const Cplx &b) 
     return __ddiv_rn(num, den);
 }
 
-__device__ __forceinline__ double exact_disc(const View &vw, int s, int v) {
+__device__ __forceinline__ double exact_disc(const double *lut, const View &vw, int s, int v) {
     int64_t g = global_of(vw, s, v);
     if (g < 0) return 0.0;                       // untouched zero buffer
-    Cplx a = exact_filtered(vw, s, v - 1, g - 1);
-    Cplx b = exact_filtered(vw, s, v, g);
+    Cplx a = exact_filtered(lut, vw, s, v - 1, g - 1);
+    Cplx b = exact_filtered(lut, vw, s, v, g);
     return exact_disc_from(a, b);
 }
 
 // quantize: IEEE sign bit
-__device__ __forceinline__ uint32_t exact_bit(const View &vw, int s, int v) {
-    return (uint32_t)((unsigned long long)__double_as_longlong(exact_disc(vw, s, v)) >> 63);
+__device__ __forceinline__ uint32_t exact_bit(const double *lut, const View &vw, int s, int v) {
+    return (uint32_t)((unsigned long long)__double_as_longlong(exact_disc(lut, vw, s, v)) >> 63);
 }
 
 }  // namespace davis

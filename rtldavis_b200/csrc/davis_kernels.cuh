@@ -14,12 +14,29 @@ struct Cand {
     uint32_t pad;
 };
 
+// One (call, index) report of a confirmed preamble before per-call dedupe
+// (Demodulator._slice, dsp.py:190-205, up to the `seen` check).
+struct alignas(16) Rec {
+    int64_t g;                 // global sample index of the preamble
+    int32_t v;                 // index into the call's virtual sample sequence
+    uint32_t stream;           // local to the pipeline stage
+    uint32_t call;
+    int32_t index;             // Packet.index
+    uint8_t data[10];          // Packet.data (on-air order)
+    uint8_t crc_ok;
+    uint8_t flags;
+    uint32_t pad[3];
+};
+static_assert(sizeof(Rec) == 48, "Rec layout");
+
 // Device-side counters of one pipeline stage (zeroed before every call).
 struct Counters {
     unsigned int n_cand;       // entries appended to the candidate list
     unsigned int n_conf;       // entries appended to the confirmed list
-    unsigned int n_hit;        // records appended to the hit buffer
-    unsigned int overflow;     // bit0 cand, bit1 conf, bit2 hit
+    unsigned int n_rec;        // records produced (before dedupe)
+    unsigned int n_hit;        // packets written to the hit buffer (after dedupe)
+    unsigned int overflow;     // bit0 cand, bit1 conf, bit2 rec/hit
+    unsigned int pad[3];
 };
 
 struct SearchParams {
@@ -29,6 +46,7 @@ struct SearchParams {
     int tiles_alloc;           // tiles per stream in the plane buffer
     int n_streams;
     unsigned int cand_cap, conf_cap, hit_cap;
+    unsigned int tbl_mask;     // dedupe hash table size - 1 (power of two)
 };
 
 constexpr int DEMOD_WARPS = 8;
@@ -40,8 +58,10 @@ void launch_search(const uint32_t *planes, const SearchParams &sp, Cand *cand, C
 void launch_precheck(const View &vw, const SearchParams &sp, const Cand *cand, Cand *conf,
                      Counters *ctr, cudaStream_t st);
 void launch_confirm(const View &vw, const SearchParams &sp, const uint32_t *planes,
-                    const Cand *conf, davis_hit *hits, Counters *ctr, int n_blocks,
-                    cudaStream_t st);
+                    const Cand *conf, Rec *recs, uint32_t *tbl, uint8_t *lost, Counters *ctr,
+                    int n_blocks, cudaStream_t st);
+void launch_finalize(const View &vw, const SearchParams &sp, const Rec *recs, const uint8_t *lost,
+                     davis_hit *hits, Counters *ctr, cudaStream_t st);
 void launch_carry(const uint8_t *carry_old, uint8_t *carry_new, size_t carry_stride, int keep,
                   const uint8_t *input, size_t input_stride, int n_new, int n_streams,
                   int64_t *blocks_done, int n_blocks, cudaStream_t st);

@@ -106,6 +106,8 @@ void launch_search(const uint32_t *planes, const SearchParams &sp, Cand *cand, C
 __global__ void __launch_bounds__(256)
 k_precheck(View vw, SearchParams sp, const Cand *__restrict__ cand, Cand *__restrict__ conf,
            Counters *ctr) {
+    __shared__ double lut[256];
+    stage_lut(lut, vw.lut);
     const unsigned int n = min(ctr->n_cand, sp.cand_cap);
     for (unsigned int i = blockIdx.x * blockDim.x + threadIdx.x; i < n;
          i += gridDim.x * blockDim.x) {
@@ -113,7 +115,7 @@ k_precheck(View vw, SearchParams sp, const Cand *__restrict__ cand, Cand *__rest
         bool pass = c.miss < 0;
         if (!pass) {
             const uint32_t want = (sp.pat_rev >> c.miss) & 1u;
-            pass = exact_bit(vw, (int)c.stream, c.v + SPS * c.miss) == want;
+            pass = exact_bit(lut, vw, (int)c.stream, c.v + SPS * c.miss) == want;
         }
         if (pass) {
             const unsigned int at = atomicAdd(&ctr->n_conf, 1u);
@@ -129,13 +131,72 @@ void launch_precheck(const View &vw, const SearchParams &sp, const Cand *cand, C
 }
 
 // ---------------------------------------------------------------------------
+// Per-call dedupe (dsp.py:203-205: within one demodulate() call a payload that
+// was already returned is skipped; "first" is the search order of dsp.py:175-186,
+// i.e. ascending (index mod 14, index)).  Done on the device with an open-
+// addressing table keyed by (stream, call, payload) whose slots hold the id of
+// the record that currently wins; a record that loses (at insertion or when it
+// is displaced later) is flagged in lost[].  Exact: keys are compared in full.
+// ---------------------------------------------------------------------------
+constexpr uint32_t TBL_EMPTY = 0xFFFFFFFFu;
+
+struct RecKey { uint32_t w[5]; };          // stream, call, data[0..9] packed, order
+
+__device__ __forceinline__ RecKey key_of(const Rec *r) {
+    // bypass L1: the record may have been written by another SM
+    const uint4 a = __ldcg(reinterpret_cast<const uint4 *>(r));        // g, v, stream
+    const uint4 b = __ldcg(reinterpret_cast<const uint4 *>(r) + 1);    // call, index, data[0..7]
+    const uint2 c = __ldcg(reinterpret_cast<const uint2 *>(r) + 4);    // data[8..9], crc, flags, pad
+    RecKey k;
+    k.w[0] = a.w;
+    k.w[1] = b.x;
+    k.w[2] = b.z;
+    k.w[3] = b.w;
+    k.w[4] = c.x & 0xFFFFu;
+    (void)a;
+    return k;
+}
+__device__ __forceinline__ uint32_t order_of(int32_t index) {
+    return ((uint32_t)(index % SPS) << 24) | (uint32_t)index;
+}
+__device__ __forceinline__ int32_t index_of(const Rec *r) {
+    return (int32_t)__ldcg(reinterpret_cast<const uint32_t *>(r) + 5);
+}
+
+__device__ void dedupe_insert(const Rec *recs, uint32_t id, uint32_t *tbl, uint32_t mask,
+                              uint8_t *lost) {
+    const RecKey me = key_of(recs + id);
+    const uint32_t my_order = order_of(index_of(recs + id));
+    uint32_t h = me.w[0] * 0x9E3779B1u;
+    h = (h ^ me.w[1]) * 0x85EBCA6Bu;
+    h = (h ^ me.w[2]) * 0xC2B2AE35u;
+    h = (h ^ me.w[3]) * 0x27D4EB2Fu;
+    h = (h ^ me.w[4]) * 0x165667B1u;
+    h = (h ^ (h >> 15)) & mask;
+    for (;;) {
+        const uint32_t cur = atomicCAS(&tbl[h], TBL_EMPTY, id);
+        if (cur == TBL_EMPTY) return;
+        const RecKey o = key_of(recs + cur);
+        if (o.w[0] == me.w[0] && o.w[1] == me.w[1] && o.w[2] == me.w[2] && o.w[3] == me.w[3] &&
+            o.w[4] == me.w[4]) {
+            if (my_order < order_of(index_of(recs + cur))) {
+                if (atomicCAS(&tbl[h], cur, id) == cur) { lost[cur] = 1; return; }
+                continue;                                    // slot changed under us: look again
+            }
+            lost[id] = 1;
+            return;
+        }
+        h = (h + 1) & mask;
+    }
+}
+
+// ---------------------------------------------------------------------------
 // k_confirm: one warp per surviving candidate.  All 80 symbols are decided in
 // fp64 in the reference's operation order; the first 16 must equal the sync
 // word.  Then: pack MSB-first (dsp.py:197-200), bit-reverse each byte and run
 // the table CRC over bytes 2..9 (protocol.py:290-297, crc.py:19-26), and emit
 // one record per reference call whose window holds the position at index <=
-// block_size (dsp.py:194), with that call's RSSI/SNR (dsp.py:207-236) and the
-// discriminator mean Parser.parse takes (protocol.py:304-310).
+// block_size (dsp.py:194), entering each into the dedupe table.
 // ---------------------------------------------------------------------------
 __device__ __forceinline__ double warp_sum(double x) {
 #pragma unroll
@@ -143,32 +204,21 @@ __device__ __forceinline__ double warp_sum(double x) {
     return x;
 }
 
-// mean |F|^2 over filtered[i0:i1) of call k, where filtered[i] = F[k*B - 1 + i]
-__device__ double mean_power(const View &vw, int s, int64_t base_g, int64_t k, int i0, int i1,
-                             int lane) {
-    double acc = 0.0;
-    for (int i = i0 + lane; i < i1; i += 32) {
-        const int64_t g = k * (int64_t)vw.block - 1 + i;
-        const Cplx f = exact_filtered(vw, s, (int)(g - base_g), g);
-        acc += f.re * f.re + f.im * f.im;
-    }
-    return warp_sum(acc) / (double)(i1 - i0);
-}
-
 constexpr int CONFIRM_WARPS = 8;
 
 __global__ void __launch_bounds__(CONFIRM_WARPS * 32)
 k_confirm(View vw, SearchParams sp, const uint32_t *__restrict__ planes,
-          const Cand *__restrict__ conf, davis_hit *__restrict__ hits, Counters *ctr,
+          const Cand *__restrict__ conf, Rec *recs, uint32_t *tbl, uint8_t *lost, Counters *ctr,
           int n_blocks) {
-    __shared__ uint16_t tbl[256];
+    __shared__ uint16_t tbl16[256];
+    __shared__ double lut[256];
     for (int i = threadIdx.x; i < 256; i += blockDim.x) {      // crc.py:28-42, poly 0x1021
         uint32_t reg = (uint32_t)i << 8;
 #pragma unroll
         for (int b = 0; b < 8; b++) reg = (reg & 0x8000u) ? ((reg << 1) ^ 0x1021u) : (reg << 1);
-        tbl[i] = (uint16_t)reg;
+        tbl16[i] = (uint16_t)reg;
     }
-    __syncthreads();
+    stage_lut(lut, vw.lut);
 
     const int lane = threadIdx.x & 31;
     const unsigned int n = min(ctr->n_conf, sp.conf_cap);
@@ -184,7 +234,7 @@ k_confirm(View vw, SearchParams sp, const uint32_t *__restrict__ planes,
             uint32_t bit = 0, fast = 0;
             if (i < PKT_SYMS) {
                 const int v = c.v + SPS * i;
-                bit = exact_bit(vw, s, v);
+                bit = exact_bit(lut, vw, s, v);
                 const int sym = v / SPS, ph = v - sym * SPS;
                 fast = (planes[((size_t)s * sp.tiles_alloc + (sym >> 5)) * PLANE_WORDS + ph] >>
                         (sym & 31)) & 1u;
@@ -193,6 +243,7 @@ k_confirm(View vw, SearchParams sp, const uint32_t *__restrict__ planes,
             disagree |= __ballot_sync(0xFFFFFFFFu, bit != fast);
         }
         if ((m[0] & 0xFFFFu) != sp.pat_rev) continue;          // not a match in float64
+        if (lane != 0) continue;
 
         // host-order byte b is the 8 symbols in arrival order, LSB first; the
         // on-air (Packet.data) byte is its bit reversal.
@@ -201,59 +252,112 @@ k_confirm(View vw, SearchParams sp, const uint32_t *__restrict__ planes,
         for (int b = 0; b < PKT_BYTES; b++) host[b] = (uint8_t)(m[b >> 2] >> (8 * (b & 3)));
         uint32_t reg = 0;
 #pragma unroll
-        for (int b = 2; b < PKT_BYTES; b++) reg = ((reg << 8) & 0xFFFFu) ^ tbl[(reg >> 8) ^ host[b]];
+        for (int b = 2; b < PKT_BYTES; b++)
+            reg = ((reg << 8) & 0xFFFFu) ^ tbl16[(reg >> 8) ^ host[b]];
 
         const int64_t B = vw.block, W = vw.window_blocks;
         const int64_t done = vw.blocks_done[s];
-        const int64_t base_g = done * B - vw.n_carry;           // global index of v = 0
-        const int64_t g = base_g + c.v;
+        const int64_t g = done * B - vw.n_carry + c.v;
         const int64_t k_hi = g / B + W - 1;
         for (int64_t k = k_hi - 1; k <= k_hi; k++) {
             const int64_t idx = g - (k - W + 1) * B;
             if (idx < 0 || idx > B || k < done || k >= done + n_blocks) continue;
-            const int q = (int)idx;
-            const int pre = SPS * PRE_SYMS;
-            // dsp.py:207-236: filtered[] holds only the call's newest block (+1)
-            const int s1 = min(q + pre, (int)B + 1);
-            const double sig = mean_power(vw, s, base_g, k, q, s1, lane);
-            const int n0 = max(0, q - pre);
-            const double noise = q > n0 ? mean_power(vw, s, base_g, k, n0, q, lane) : 1e-9;
-            // protocol.py:304-310: discriminated[] spans blocks k-1 and k
-            double dsum = 0.0;
-            for (int t = lane; t < pre; t += 32) {
-                const int64_t gd = (k - 1) * B + q + t;
-                dsum += exact_disc(vw, s, (int)(gd - base_g));
-            }
-            dsum = warp_sum(dsum);
-            if (lane == 0) {
-                const unsigned int at = atomicAdd(&ctr->n_hit, 1u);
-                if (at < sp.hit_cap) {
-                    davis_hit h;
-                    h.position = g;
-                    h.stream = (uint32_t)(vw.stream0 + s);
-                    h.call = (uint32_t)k;
-                    h.index = q;
+            const unsigned int at = atomicAdd(&ctr->n_rec, 1u);
+            if (at >= sp.hit_cap) { atomicOr(&ctr->overflow, 4u); continue; }
+            Rec r;
+            r.g = g;
+            r.v = c.v;
+            r.stream = (uint32_t)s;
+            r.call = (uint32_t)k;
+            r.index = (int32_t)idx;
 #pragma unroll
-                    for (int b = 0; b < PKT_BYTES; b++)
-                        h.data[b] = (uint8_t)(__brev((uint32_t)host[b]) >> 24);
-                    h.crc_ok = reg == 0;
-                    h.flags = disagree ? 1 : 0;
-                    h.rssi = sig > 0.0 ? 10.0 * log10(sig) : -120.0;
-                    h.snr = noise > 0.0 ? 10.0 * log10(sig / noise) : 50.0;
-                    h.disc_mean = dsum / (double)pre;
-                    hits[at] = h;
-                } else {
-                    atomicOr(&ctr->overflow, 4u);
-                }
-            }
+            for (int b = 0; b < PKT_BYTES; b++) r.data[b] = (uint8_t)(__brev((uint32_t)host[b]) >> 24);
+            r.crc_ok = reg == 0;
+            r.flags = disagree ? 1 : 0;
+            r.pad[0] = r.pad[1] = r.pad[2] = 0;
+            recs[at] = r;
+            __threadfence();                                   // publish before the id is visible
+            dedupe_insert(recs, at, tbl, sp.tbl_mask, lost);
         }
     }
 }
 
 void launch_confirm(const View &vw, const SearchParams &sp, const uint32_t *planes,
-                    const Cand *conf, davis_hit *hits, Counters *ctr, int n_blocks,
-                    cudaStream_t st) {
-    k_confirm<<<148 * 2, CONFIRM_WARPS * 32, 0, st>>>(vw, sp, planes, conf, hits, ctr, n_blocks);
+                    const Cand *conf, Rec *recs, uint32_t *tbl, uint8_t *lost, Counters *ctr,
+                    int n_blocks, cudaStream_t st) {
+    k_confirm<<<148 * 4, CONFIRM_WARPS * 32, 0, st>>>(vw, sp, planes, conf, recs, tbl, lost, ctr,
+                                                      n_blocks);
+}
+
+// ---------------------------------------------------------------------------
+// k_finalize: one warp per record that survived the dedupe.  Adds what the
+// reference attaches to a returned Packet: RSSI/SNR (dsp.py:207-236, with its
+// one-block `filtered` buffer indexed by two-block window positions) and the
+// discriminator mean Parser.parse takes (protocol.py:304-310), all in fp64.
+// ---------------------------------------------------------------------------
+// mean |F|^2 over filtered[i0:i1) of call k, where filtered[i] = F[k*B - 1 + i]
+__device__ double mean_power(const double *lut, const View &vw, int s, int64_t base_g, int64_t k,
+                             int i0, int i1, int lane) {
+    double acc = 0.0;
+    for (int i = i0 + lane; i < i1; i += 32) {
+        const int64_t g = k * (int64_t)vw.block - 1 + i;
+        const Cplx f = exact_filtered(lut, vw, s, (int)(g - base_g), g);
+        acc += f.re * f.re + f.im * f.im;
+    }
+    return warp_sum(acc) / (double)(i1 - i0);
+}
+
+__global__ void __launch_bounds__(CONFIRM_WARPS * 32)
+k_finalize(View vw, SearchParams sp, const Rec *__restrict__ recs,
+           const uint8_t *__restrict__ lost, davis_hit *__restrict__ hits, Counters *ctr) {
+    __shared__ double lut[256];
+    stage_lut(lut, vw.lut);
+    const int lane = threadIdx.x & 31;
+    const unsigned int n = min(ctr->n_rec, sp.hit_cap);
+    const unsigned int warps = gridDim.x * CONFIRM_WARPS;
+    for (unsigned int ri = blockIdx.x * CONFIRM_WARPS + (threadIdx.x >> 5); ri < n; ri += warps) {
+        if (lost[ri]) continue;
+        const Rec r = recs[ri];
+        const int s = (int)r.stream;
+        const int64_t B = vw.block;
+        const int64_t base_g = r.g - r.v;                      // global index of v = 0
+        const int64_t k = r.call;
+        const int q = r.index;
+        const int pre = SPS * PRE_SYMS;
+        // dsp.py:207-236: filtered[] holds only the call's newest block (+1)
+        const int s1 = min(q + pre, (int)B + 1);
+        const double sig = mean_power(lut, vw, s, base_g, k, q, s1, lane);
+        const int n0 = max(0, q - pre);
+        const double noise = q > n0 ? mean_power(lut, vw, s, base_g, k, n0, q, lane) : 1e-9;
+        // protocol.py:304-310: discriminated[] spans blocks k-1 and k
+        double dsum = 0.0;
+        for (int t = lane; t < pre; t += 32) {
+            const int64_t gd = (k - 1) * B + q + t;
+            dsum += exact_disc(lut, vw, s, (int)(gd - base_g));
+        }
+        dsum = warp_sum(dsum);
+        if (lane == 0) {
+            const unsigned int at = atomicAdd(&ctr->n_hit, 1u);   // <= n_rec <= hit_cap
+            davis_hit h;
+            h.position = r.g;
+            h.stream = (uint32_t)(vw.stream0 + s);
+            h.call = r.call;
+            h.index = q;
+#pragma unroll
+            for (int b = 0; b < PKT_BYTES; b++) h.data[b] = r.data[b];
+            h.crc_ok = r.crc_ok;
+            h.flags = r.flags;
+            h.rssi = sig > 0.0 ? 10.0 * log10(sig) : -120.0;
+            h.snr = noise > 0.0 ? 10.0 * log10(sig / noise) : 50.0;
+            h.disc_mean = dsum / (double)pre;
+            hits[at] = h;
+        }
+    }
+}
+
+void launch_finalize(const View &vw, const SearchParams &sp, const Rec *recs, const uint8_t *lost,
+                     davis_hit *hits, Counters *ctr, cudaStream_t st) {
+    k_finalize<<<148 * 4, CONFIRM_WARPS * 32, 0, st>>>(vw, sp, recs, lost, hits, ctr);
 }
 
 // ---------------------------------------------------------------------------
@@ -297,8 +401,10 @@ void launch_carry(const uint8_t *carry_old, uint8_t *carry_new, size_t carry_str
 // debug / parity taps
 // ---------------------------------------------------------------------------
 __global__ void k_exact_disc(View vw, int stream, int v0, int n, double *out) {
+    __shared__ double lut[256];
+    stage_lut(lut, vw.lut);
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) out[i] = exact_disc(vw, stream, v0 + i);
+    if (i < n) out[i] = exact_disc(lut, vw, stream, v0 + i);
 }
 
 void launch_exact_disc(const View &vw, int stream, int v0, int n, double *out, cudaStream_t st) {

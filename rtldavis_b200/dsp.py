@@ -158,6 +158,8 @@ class BatchDemodulator:
         if nbytes == 0 or nbytes % (2 * B):
             raise ValueError("Incompatible array sizes")
         n_blocks = nbytes // (2 * B)
+        if n_blocks > self.max_blocks:
+            raise ValueError(f"{n_blocks} blocks per call exceed max_blocks={self.max_blocks}")
         self._keepalive = iq
         rc = self._L.davis_demod_u8(self._h, ptr, nbytes, stride, n_blocks,
                                     C.c_void_p(cuda_stream) if cuda_stream else None)
