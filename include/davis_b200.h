@@ -94,6 +94,10 @@ typedef struct davis_stats {
     float total_ms;           /* first kernel start to last kernel end               */
     uint64_t h2d_bytes;       /* bytes copied host->device by the call               */
     uint64_t d2h_bytes;       /* bytes copied device->host by the fetch              */
+    float host_submit_ms;     /* host time inside davis_demod_u8 (enqueue only)      */
+    float host_wait_ms;       /* host time the fetch spent waiting for the device    */
+    float host_copy_ms;       /* host time copying packet records back               */
+    float host_sort_ms;       /* host time ordering the records (dsp.py:175-186)     */
 } davis_stats;
 
 DAVIS_API int davis_abi_version(void);

@@ -27,7 +27,9 @@ class DavisStats(C.Structure):
     _fields_ = [("samples", C.c_uint64), ("launches", C.c_uint64), ("candidates", C.c_uint64),
                 ("confirmed", C.c_uint64), ("records", C.c_uint64), ("demod_ms", C.c_float),
                 ("search_ms", C.c_float), ("finish_ms", C.c_float), ("total_ms", C.c_float),
-                ("h2d_bytes", C.c_uint64), ("d2h_bytes", C.c_uint64)]
+                ("h2d_bytes", C.c_uint64), ("d2h_bytes", C.c_uint64),
+                ("host_submit_ms", C.c_float), ("host_wait_ms", C.c_float),
+                ("host_copy_ms", C.c_float), ("host_sort_ms", C.c_float)]
 
 
 HIT_DTYPE = np.dtype([("position", "<i8"), ("stream", "<u4"), ("call", "<u4"), ("index", "<i4"),

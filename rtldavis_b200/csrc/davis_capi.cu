@@ -6,6 +6,7 @@
 // (ordering of Demodulator._search, dsp.py:171-188; dedupe of _slice,
 // dsp.py:203-205).
 #include <algorithm>
+#include <chrono>
 #include <cstdio>
 #include <cstring>
 #include <new>
@@ -27,6 +28,9 @@ struct Stage {
     Rec *recs = nullptr;         size_t recs_cap = 0;
     uint32_t *tbl = nullptr;     size_t tbl_size = 0;        // dedupe table, power of two
     uint8_t *lost = nullptr;     size_t lost_cap = 0;
+    davis_hit *tmp = nullptr;    size_t tmp_cap = 0;         // packets before ordering
+    unsigned int *bucket = nullptr;  size_t bucket_cap = 0;
+    unsigned int *per_stream = nullptr;  size_t per_stream_cap = 0;   // count | start | fill
     Counters *ctr = nullptr;
     int last_group = -1;
     int tiles_alloc = 0;
@@ -68,6 +72,11 @@ struct davis_handle {
 };
 
 namespace {
+
+double now_ms() {
+    return std::chrono::duration<double, std::milli>(
+               std::chrono::steady_clock::now().time_since_epoch()).count();
+}
 
 int fail(davis_handle *h, int code, const std::string &msg) {
     if (h) h->err = msg;
@@ -114,6 +123,9 @@ int prepare_stage(davis_handle *h, Stage &st, int ns, int n_blocks, size_t stagi
     st.conf_cap = (unsigned int)have;
     if ((rc = grow(h, &st.recs, &st.recs_cap, rec_cap))) return rc;
     if ((rc = grow(h, &st.lost, &st.lost_cap, rec_cap))) return rc;
+    if ((rc = grow(h, &st.tmp, &st.tmp_cap, rec_cap))) return rc;
+    if ((rc = grow(h, &st.bucket, &st.bucket_cap, rec_cap))) return rc;
+    if ((rc = grow(h, &st.per_stream, &st.per_stream_cap, 3 * (size_t)ns + 4))) return rc;
     size_t tbl = 1024;
     while (tbl < 2 * rec_cap) tbl <<= 1;                       // load factor <= 0.5
     if (st.tbl_size < tbl) {
@@ -182,7 +194,11 @@ int run_group(davis_handle *h, Stage &stage, Group &g, int gi, const uint8_t *de
     launch_precheck(vw, sp, stage.cand, stage.conf, stage.ctr, st);
     launch_confirm(vw, sp, stage.planes, stage.conf, stage.recs, stage.tbl, stage.lost, stage.ctr,
                    n_blocks, st);
-    launch_finalize(vw, sp, stage.recs, stage.lost, h->d_hits + g.hit_off, stage.ctr, st);
+    unsigned int *count = stage.per_stream, *start = count + g.ns, *fill = start + g.ns + 1;
+    CU(cudaMemsetAsync(count, 0, sizeof(unsigned int) * g.ns, st));
+    launch_finalize(vw, sp, stage.recs, stage.lost, stage.tmp, count, stage.ctr, st);
+    launch_order(stage.tmp, stage.ctr, g.s0, g.ns, count, start, fill, stage.bucket,
+                 h->d_hits + g.hit_off, st);
     launch_carry(h->carry[h->cur] + (size_t)g.s0 * h->carry_stride,
                  h->carry[h->cur ^ 1] + (size_t)g.s0 * h->carry_stride, h->carry_stride, h->n_keep,
                  dev_input, input_stride, n_blocks * h->B, g.ns, h->d_blocks_done + g.s0, n_blocks,
@@ -192,16 +208,8 @@ int run_group(davis_handle *h, Stage &stage, Group &g, int gi, const uint8_t *de
     CU(cudaEventRecord(g.ev[4], st));
     CU(cudaGetLastError());
     stage.last_group = gi;
-    h->stats.launches += 5 + (uint64_t)((g.ns + 65534) / 65535);
+    h->stats.launches += 8 + (uint64_t)((g.ns + 65534) / 65535);
     return DAVIS_OK;
-}
-
-bool hit_less(const davis_hit &a, const davis_hit &b) {
-    if (a.stream != b.stream) return a.stream < b.stream;
-    if (a.call != b.call) return a.call < b.call;
-    const int pa = a.index % SPS, pb = b.index % SPS;     // dsp.py:175: offset-major
-    if (pa != pb) return pa < pb;
-    return a.index < b.index;
 }
 
 }  // namespace
@@ -289,6 +297,9 @@ int davis_destroy(davis_handle *h) {
         if (s.recs) cudaFree(s.recs);
         if (s.tbl) cudaFree(s.tbl);
         if (s.lost) cudaFree(s.lost);
+        if (s.tmp) cudaFree(s.tmp);
+        if (s.bucket) cudaFree(s.bucket);
+        if (s.per_stream) cudaFree(s.per_stream);
         if (s.ctr) cudaFree(s.ctr);
         if (s.st) cudaStreamDestroy(s.st);
     }
@@ -329,6 +340,7 @@ int davis_demod_u8(davis_handle *h, const uint8_t *iq, size_t bytes_per_stream,
     if (h->n_streams > 1 && stream_stride < bytes_per_stream)
         return fail(h, DAVIS_E_SIZE, "stream_stride smaller than bytes_per_stream");
     if (h->queued) return fail(h, DAVIS_E_STATE, "previous call not fetched");
+    const double t_submit = now_ms();
     CU(cudaSetDevice(h->device));
 
     cudaPointerAttributes attr;
@@ -405,6 +417,7 @@ int davis_demod_u8(davis_handle *h, const uint8_t *iq, size_t bytes_per_stream,
     for (auto &b : h->h_blocks_done) b += n_blocks;
     h->queued = true;
     h->queued_blocks = n_blocks;
+    h->stats.host_submit_ms = (float)(now_ms() - t_submit);
     return DAVIS_OK;
 }
 
@@ -418,9 +431,12 @@ int davis_fetch_hits(davis_handle *h, davis_hit *out, size_t cap, size_t *n) {
     if (h->queued) {
         h->results.clear();
         float demod = 0, search = 0, finish = 0;
+        double t_wait = 0, t_copy = 0;
         for (size_t gi = 0; gi < h->groups.size(); gi++) {
             Group &g = h->groups[gi];
+            const double t0 = now_ms();
             CU(cudaEventSynchronize(g.ev[4]));
+            t_wait += now_ms() - t0;
             const Counters c = h->h_ctr[gi];
             float ms;
             CU(cudaEventElapsedTime(&ms, g.ev[0], g.ev[1])); demod += ms;
@@ -440,8 +456,10 @@ int davis_fetch_hits(davis_handle *h, davis_hit *out, size_t cap, size_t *n) {
             const size_t at = h->results.size();
             h->results.resize(at + c.n_hit);
             if (c.n_hit) {
+                const double t1 = now_ms();
                 CU(cudaMemcpy(h->results.data() + at, h->d_hits + g.hit_off,
                               sizeof(davis_hit) * c.n_hit, cudaMemcpyDeviceToHost));
+                t_copy += now_ms() - t1;
                 h->stats.d2h_bytes += sizeof(davis_hit) * c.n_hit;
             }
             h->stats.d2h_bytes += sizeof(Counters);
@@ -459,21 +477,12 @@ int davis_fetch_hits(davis_handle *h, davis_hit *out, size_t cap, size_t *n) {
             }
             h->stats.total_ms = first_to_last;
         }
-        // The device already applied the per-call dedupe (dsp.py:203-205); what is
-        // left is the reference's order: stream, call, then (index mod 14, index)
-        // (dsp.py:175-186).  Bucket by stream, then sort the short buckets.
-        {
-            const size_t n_res = h->results.size();
-            std::vector<uint32_t> start((size_t)h->n_streams + 1, 0);
-            for (const davis_hit &r : h->results) start[r.stream + 1]++;
-            for (int s = 0; s < h->n_streams; s++) start[s + 1] += start[s];
-            std::vector<davis_hit> sorted(n_res);
-            std::vector<uint32_t> fill(start.begin(), start.end() - 1);
-            for (const davis_hit &r : h->results) sorted[fill[r.stream]++] = r;
-            for (int s = 0; s < h->n_streams; s++)
-                std::sort(sorted.begin() + start[s], sorted.begin() + start[s + 1], hit_less);
-            h->results.swap(sorted);
-        }
+        // Nothing to do on the host: the device applied the per-call dedupe
+        // (dsp.py:203-205) and delivered every group in (stream, call, index mod 14,
+        // index) order (dsp.py:175-186); groups hold ascending stream ranges.
+        h->stats.host_wait_ms = (float)t_wait;
+        h->stats.host_copy_ms = (float)t_copy;
+        h->stats.host_sort_ms = 0.0f;
         h->queued = false;
         h->have_results = true;
     } else if (!h->have_results) {

@@ -64,21 +64,79 @@ __device__ __forceinline__ int64_t global_of(const View &vw, int s, int v) {
 
 // ---------------------------------------------------------------------------
 // fp64, reference order.  No FMA contraction anywhere (explicit _rn intrinsics).
-// ---------------------------------------------------------------------------
-struct Cplx { double re, im; };
-
-// rotated sample r[g] = lut(u) * j^(g mod 4); zero before the stream began
+//
+// The evaluators are templated on a sample source `Src` with
+//     uchar2 at(int v) const      raw (I, Q) bytes of V index v (v >= 0)
+//     int64_t g0                  global sample index of v = 0
+// GlobalSrc reads the carry/input buffers directly; SpanSrc reads a span that a
+// warp staged in shared memory with coalesced 16-byte loads.
 // `lut` is the reference's 256-entry table (u - 127.4) / 127.6 (dsp.py:26), built
 // once on the host in float64 and staged in shared memory by every kernel that
 // evaluates the exact form (a divide per sample would dominate those kernels).
-__device__ __forceinline__ Cplx exact_rotated(const double *lut, const View &vw, int s, int v,
-                                              int64_t g) {
+// ---------------------------------------------------------------------------
+struct Cplx { double re, im; };
+
+struct GlobalSrc {
+    const uint8_t *carry, *input;
+    int n_carry;
+    int64_t g0;
+    __device__ __forceinline__ GlobalSrc(const View &vw, int s)
+        : carry(vw.carry + (size_t)s * vw.carry_stride),
+          input(vw.input + (size_t)s * vw.input_stride),
+          n_carry(vw.n_carry),
+          g0(vw.blocks_done[s] * (int64_t)vw.block - vw.n_carry) {}
+    __device__ __forceinline__ uchar2 at(int v) const {
+        const uint8_t *p = v < n_carry ? carry + 2 * (size_t)v : input + 2 * (size_t)(v - n_carry);
+        return *reinterpret_cast<const uchar2 *>(p);
+    }
+};
+
+struct SpanSrc {
+    const uint8_t *base;      // shared memory; byte 0 holds V index v0
+    int v0;
+    int64_t g0;
+    __device__ __forceinline__ uchar2 at(int v) const {
+        return *reinterpret_cast<const uchar2 *>(base + 2 * (v - v0));
+    }
+};
+
+// A warp copies V samples [v_begin, v_begin + n) of stream s into `dst` (shared,
+// 16-byte aligned, room for 2*n + 32 bytes) and returns the source describing it.
+// Chunks before the start of V are zero-filled (they are only ever addressed for
+// g < 0, where the evaluators substitute the zero history anyway).
+__device__ __forceinline__ SpanSrc stage_span(const View &vw, int s, int v_begin, int n,
+                                              uint8_t *dst, int lane) {
+    const long long b0 = (2LL * v_begin) & ~15LL;              // floor to a 16-byte chunk
+    const long long b1 = 2LL * (v_begin + n);
+    const long long carry_bytes = 2LL * vw.n_carry, total = carry_bytes + 2LL * vw.n_new;
+    const uint8_t *carry = vw.carry + (size_t)s * vw.carry_stride;
+    const uint8_t *input = vw.input + (size_t)s * vw.input_stride;
+    const int chunks = (int)((b1 - b0 + 15) >> 4);
+    for (int c = lane; c < chunks; c += 32) {
+        const long long off = b0 + 16LL * c;
+        uint4 val = make_uint4(0u, 0u, 0u, 0u);
+        if (off >= 0 && off < total)
+            val = __ldg(reinterpret_cast<const uint4 *>(off < carry_bytes ? carry + off
+                                                                         : input + (off - carry_bytes)));
+        reinterpret_cast<uint4 *>(dst)[c] = val;
+    }
+    __syncwarp();
+    SpanSrc src;
+    src.base = dst;
+    src.v0 = (int)(b0 >> 1);
+    src.g0 = vw.blocks_done[s] * (int64_t)vw.block - vw.n_carry;
+    return src;
+}
+
+// rotated sample r[g] = lut(u) * j^(g mod 4); zero before the stream began
+template <class Src>
+__device__ __forceinline__ Cplx exact_rotated(const double *lut, const Src &src, int v) {
     Cplx r{0.0, 0.0};
+    const int64_t g = src.g0 + v;
     if (g < 0 || v < 0) return r;
-    const uint8_t *p = sample_ptr(vw, s, v);
-    const uchar2 u = *reinterpret_cast<const uchar2 *>(p);
-    double xr = lut[u.x];
-    double xi = lut[u.y];
+    const uchar2 u = src.at(v);
+    const double xr = lut[u.x];
+    const double xi = lut[u.y];
     switch ((int)(g & 3)) {
     case 0: r.re = xr;  r.im = xi;  break;
     case 1: r.re = -xi; r.im = xr;  break;
@@ -89,38 +147,69 @@ __device__ __forceinline__ Cplx exact_rotated(const double *lut, const View &vw,
 }
 
 // F[g] = sum_m taps[m] * r[g-9+m], summed m = 0..8
-__device__ __forceinline__ Cplx exact_filtered(const double *lut, const View &vw, int s, int v,
-                                               int64_t g) {
+template <class Src>
+__device__ __forceinline__ Cplx exact_filtered(const double *lut, const Src &src, int v) {
     const double taps[9] = {DAVIS_C0, DAVIS_C1, DAVIS_C2, DAVIS_C3, DAVIS_C4,
                             DAVIS_C3, DAVIS_C2, DAVIS_C1, DAVIS_C0};
     Cplx f{0.0, 0.0};
 #pragma unroll
     for (int m = 0; m < 9; m++) {
-        Cplx r = exact_rotated(lut, vw, s, v - 9 + m, g - 9 + m);
+        const Cplx r = exact_rotated(lut, src, v - 9 + m);
         f.re = __dadd_rn(f.re, __dmul_rn(taps[m], r.re));
         f.im = __dadd_rn(f.im, __dmul_rn(taps[m], r.im));
     }
     return f;
 }
 
-// D[g] = (Im a * Re b - Re a * Im b) / (|a|^2 + 1e-10), a = F[g-1], b = F[g]
-__device__ __forceinline__ double exact_disc_from(const Cplx &a, const Cplx &b) {
-    double num = __dsub_rn(__dmul_rn(a.im, b.re), __dmul_rn(a.re, b.im));
-    double den = __dadd_rn(__dadd_rn(__dmul_rn(a.re, a.re), __dmul_rn(a.im, a.im)), 1e-10);
-    return __ddiv_rn(num, den);
+// numerator of D[g]: Im a * Re b - Re a * Im b,  a = F[g-1], b = F[g]
+__device__ __forceinline__ double exact_cross(const Cplx &a, const Cplx &b) {
+    return __dsub_rn(__dmul_rn(a.im, b.re), __dmul_rn(a.re, b.im));
 }
 
-__device__ __forceinline__ double exact_disc(const double *lut, const View &vw, int s, int v) {
-    int64_t g = global_of(vw, s, v);
-    if (g < 0) return 0.0;                       // untouched zero buffer
-    Cplx a = exact_filtered(lut, vw, s, v - 1, g - 1);
-    Cplx b = exact_filtered(lut, vw, s, v, g);
+// D[g] = cross / (|a|^2 + 1e-10)
+__device__ __forceinline__ double exact_disc_from(const Cplx &a, const Cplx &b) {
+    const double den = __dadd_rn(__dadd_rn(__dmul_rn(a.re, a.re), __dmul_rn(a.im, a.im)), 1e-10);
+    return __ddiv_rn(exact_cross(a, b), den);
+}
+
+// a = F[g-1], b = F[g] from one pass over the ten samples they share; each sum
+// runs m = 0..8 exactly as exact_filtered does.
+template <class Src>
+__device__ __forceinline__ void exact_pair(const double *lut, const Src &src, int v, Cplx &a,
+                                           Cplx &b) {
+    const double taps[9] = {DAVIS_C0, DAVIS_C1, DAVIS_C2, DAVIS_C3, DAVIS_C4,
+                            DAVIS_C3, DAVIS_C2, DAVIS_C1, DAVIS_C0};
+    a = Cplx{0.0, 0.0};
+    b = Cplx{0.0, 0.0};
+    Cplx prev = exact_rotated(lut, src, v - 10);
+#pragma unroll
+    for (int m = 0; m < 9; m++) {
+        const Cplx cur = exact_rotated(lut, src, v - 9 + m);
+        a.re = __dadd_rn(a.re, __dmul_rn(taps[m], prev.re));
+        a.im = __dadd_rn(a.im, __dmul_rn(taps[m], prev.im));
+        b.re = __dadd_rn(b.re, __dmul_rn(taps[m], cur.re));
+        b.im = __dadd_rn(b.im, __dmul_rn(taps[m], cur.im));
+        prev = cur;
+    }
+}
+
+template <class Src>
+__device__ __forceinline__ double exact_disc(const double *lut, const Src &src, int v) {
+    if (src.g0 + v < 0) return 0.0;              // untouched zero buffer
+    Cplx a, b;
+    exact_pair(lut, src, v, a, b);
     return exact_disc_from(a, b);
 }
 
-// quantize: IEEE sign bit
-__device__ __forceinline__ uint32_t exact_bit(const double *lut, const View &vw, int s, int v) {
-    return (uint32_t)((unsigned long long)__double_as_longlong(exact_disc(lut, vw, s, v)) >> 63);
+// quantize: IEEE sign bit of D[g].  The denominator is positive and finite, so
+// the quotient (even when it underflows to a signed zero) carries the sign bit
+// of the numerator: the division is skipped.
+template <class Src>
+__device__ __forceinline__ uint32_t exact_bit(const double *lut, const Src &src, int v) {
+    if (src.g0 + v < 0) return 0u;               // +0.0 in the zero-initialised buffer
+    Cplx a, b;
+    exact_pair(lut, src, v, a, b);
+    return (uint32_t)((unsigned long long)__double_as_longlong(exact_cross(a, b)) >> 63);
 }
 
 }  // namespace davis

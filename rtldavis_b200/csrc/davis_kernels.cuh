@@ -61,7 +61,10 @@ void launch_confirm(const View &vw, const SearchParams &sp, const uint32_t *plan
                     const Cand *conf, Rec *recs, uint32_t *tbl, uint8_t *lost, Counters *ctr,
                     int n_blocks, cudaStream_t st);
 void launch_finalize(const View &vw, const SearchParams &sp, const Rec *recs, const uint8_t *lost,
-                     davis_hit *hits, Counters *ctr, cudaStream_t st);
+                     davis_hit *hits, unsigned int *per_stream, Counters *ctr, cudaStream_t st);
+void launch_order(const davis_hit *tmp, const Counters *ctr, int stream0, int n_streams,
+                  unsigned int *per_stream, unsigned int *start, unsigned int *fill,
+                  unsigned int *bucket, davis_hit *out, cudaStream_t st);
 void launch_carry(const uint8_t *carry_old, uint8_t *carry_new, size_t carry_stride, int keep,
                   const uint8_t *input, size_t input_stride, int n_new, int n_streams,
                   int64_t *blocks_done, int n_blocks, cudaStream_t st);

@@ -115,7 +115,7 @@ k_precheck(View vw, SearchParams sp, const Cand *__restrict__ cand, Cand *__rest
         bool pass = c.miss < 0;
         if (!pass) {
             const uint32_t want = (sp.pat_rev >> c.miss) & 1u;
-            pass = exact_bit(lut, vw, (int)c.stream, c.v + SPS * c.miss) == want;
+            pass = exact_bit(lut, GlobalSrc(vw, (int)c.stream), c.v + SPS * c.miss) == want;
         }
         if (pass) {
             const unsigned int at = atomicAdd(&ctr->n_conf, 1u);
@@ -210,8 +210,10 @@ __global__ void __launch_bounds__(CONFIRM_WARPS * 32)
 k_confirm(View vw, SearchParams sp, const uint32_t *__restrict__ planes,
           const Cand *__restrict__ conf, Rec *recs, uint32_t *tbl, uint8_t *lost, Counters *ctr,
           int n_blocks) {
+    constexpr int SPAN = SPS * PKT_SYMS + 16;                  // 80 symbols + FIR history
     __shared__ uint16_t tbl16[256];
     __shared__ double lut[256];
+    __shared__ uint4 span_mem[CONFIRM_WARPS][(2 * SPAN + 32 + 15) / 16];
     for (int i = threadIdx.x; i < 256; i += blockDim.x) {      // crc.py:28-42, poly 0x1021
         uint32_t reg = (uint32_t)i << 8;
 #pragma unroll
@@ -226,6 +228,9 @@ k_confirm(View vw, SearchParams sp, const uint32_t *__restrict__ planes,
     for (unsigned int ci = blockIdx.x * CONFIRM_WARPS + (threadIdx.x >> 5); ci < n; ci += warps) {
         const Cand c = conf[ci];
         const int s = (int)c.stream;
+        __syncwarp();                                          // previous span fully consumed
+        const SpanSrc src = stage_span(vw, s, c.v - 10, SPAN,
+                                       reinterpret_cast<uint8_t *>(span_mem[threadIdx.x >> 5]), lane);
         uint32_t m[3];
         uint32_t disagree = 0;
 #pragma unroll
@@ -234,7 +239,7 @@ k_confirm(View vw, SearchParams sp, const uint32_t *__restrict__ planes,
             uint32_t bit = 0, fast = 0;
             if (i < PKT_SYMS) {
                 const int v = c.v + SPS * i;
-                bit = exact_bit(lut, vw, s, v);
+                bit = exact_bit(lut, src, v);
                 const int sym = v / SPS, ph = v - sym * SPS;
                 fast = (planes[((size_t)s * sp.tiles_alloc + (sym >> 5)) * PLANE_WORDS + ph] >>
                         (sym & 31)) & 1u;
@@ -295,49 +300,60 @@ void launch_confirm(const View &vw, const SearchParams &sp, const uint32_t *plan
 // one-block `filtered` buffer indexed by two-block window positions) and the
 // discriminator mean Parser.parse takes (protocol.py:304-310), all in fp64.
 // ---------------------------------------------------------------------------
-// mean |F|^2 over filtered[i0:i1) of call k, where filtered[i] = F[k*B - 1 + i]
-__device__ double mean_power(const double *lut, const View &vw, int s, int64_t base_g, int64_t k,
-                             int i0, int i1, int lane) {
+// sum of |F|^2 over V indices [v0, v1)
+__device__ double power_sum(const double *lut, const SpanSrc &src, int v0, int v1, int lane) {
     double acc = 0.0;
-    for (int i = i0 + lane; i < i1; i += 32) {
-        const int64_t g = k * (int64_t)vw.block - 1 + i;
-        const Cplx f = exact_filtered(lut, vw, s, (int)(g - base_g), g);
+    for (int v = v0 + lane; v < v1; v += 32) {
+        const Cplx f = exact_filtered(lut, src, v);
         acc += f.re * f.re + f.im * f.im;
     }
-    return warp_sum(acc) / (double)(i1 - i0);
+    return warp_sum(acc);
 }
 
 __global__ void __launch_bounds__(CONFIRM_WARPS * 32)
 k_finalize(View vw, SearchParams sp, const Rec *__restrict__ recs,
-           const uint8_t *__restrict__ lost, davis_hit *__restrict__ hits, Counters *ctr) {
+           const uint8_t *__restrict__ lost, davis_hit *__restrict__ hits,
+           unsigned int *__restrict__ per_stream, Counters *ctr) {
+    constexpr int PRE = SPS * PRE_SYMS;                        // 224
+    constexpr int SPAN_P = 2 * PRE + 16, SPAN_D = PRE + 16;
     __shared__ double lut[256];
+    __shared__ uint4 mem_p[CONFIRM_WARPS][(2 * SPAN_P + 32 + 15) / 16];
+    __shared__ uint4 mem_d[CONFIRM_WARPS][(2 * SPAN_D + 32 + 15) / 16];
     stage_lut(lut, vw.lut);
-    const int lane = threadIdx.x & 31;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const unsigned int n = min(ctr->n_rec, sp.hit_cap);
     const unsigned int warps = gridDim.x * CONFIRM_WARPS;
-    for (unsigned int ri = blockIdx.x * CONFIRM_WARPS + (threadIdx.x >> 5); ri < n; ri += warps) {
+    for (unsigned int ri = blockIdx.x * CONFIRM_WARPS + warp; ri < n; ri += warps) {
         if (lost[ri]) continue;
         const Rec r = recs[ri];
         const int s = (int)r.stream;
-        const int64_t B = vw.block;
-        const int64_t base_g = r.g - r.v;                      // global index of v = 0
-        const int64_t k = r.call;
+        const int B = vw.block;
         const int q = r.index;
-        const int pre = SPS * PRE_SYMS;
-        // dsp.py:207-236: filtered[] holds only the call's newest block (+1)
-        const int s1 = min(q + pre, (int)B + 1);
-        const double sig = mean_power(lut, vw, s, base_g, k, q, s1, lane);
-        const int n0 = max(0, q - pre);
-        const double noise = q > n0 ? mean_power(lut, vw, s, base_g, k, n0, q, lane) : 1e-9;
-        // protocol.py:304-310: discriminated[] spans blocks k-1 and k
+        // V index of window position 0 of call r.call: the preamble sits at r.v = w0 + q
+        const int w0 = r.v - q;
+        // dsp.py:207-236: `filtered` holds only the call's newest block (+1 carried
+        // sample), filtered[i] = F[call*B - 1 + i], while q indexes the W-block
+        // window; V index of filtered[i] is w0 + (W-1)*B - 1 + i.
+        const int f0 = w0 + (vw.window_blocks - 1) * B - 1;
+        const int s1 = min(q + PRE, B + 1);                    // slice end is clipped by numpy
+        const int n0 = max(0, q - PRE);
+        __syncwarp();
+        const SpanSrc sp_p = stage_span(vw, s, f0 + n0 - 10, s1 - n0 + 10,
+                                        reinterpret_cast<uint8_t *>(mem_p[warp]), lane);
+        // protocol.py:304-310: discriminated[] spans the window's last two blocks;
+        // discriminated[i] = D[(call-1)*B + i], V index w0 + (W-2)*B + i.
+        const int d0 = w0 + (vw.window_blocks - 2) * B + q;
+        const SpanSrc sp_d = stage_span(vw, s, d0 - 11, PRE + 11,
+                                        reinterpret_cast<uint8_t *>(mem_d[warp]), lane);
+        const double sig = power_sum(lut, sp_p, f0 + q, f0 + s1, lane) / (double)(s1 - q);
+        const double noise = q > n0 ? power_sum(lut, sp_p, f0 + n0, f0 + q, lane) / (double)(q - n0)
+                                    : 1e-9;
         double dsum = 0.0;
-        for (int t = lane; t < pre; t += 32) {
-            const int64_t gd = (k - 1) * B + q + t;
-            dsum += exact_disc(lut, vw, s, (int)(gd - base_g));
-        }
+        for (int t = lane; t < PRE; t += 32) dsum += exact_disc(lut, sp_d, d0 + t);
         dsum = warp_sum(dsum);
         if (lane == 0) {
             const unsigned int at = atomicAdd(&ctr->n_hit, 1u);   // <= n_rec <= hit_cap
+            atomicAdd(&per_stream[s], 1u);
             davis_hit h;
             h.position = r.g;
             h.stream = (uint32_t)(vw.stream0 + s);
@@ -349,15 +365,120 @@ k_finalize(View vw, SearchParams sp, const Rec *__restrict__ recs,
             h.flags = r.flags;
             h.rssi = sig > 0.0 ? 10.0 * log10(sig) : -120.0;
             h.snr = noise > 0.0 ? 10.0 * log10(sig / noise) : 50.0;
-            h.disc_mean = dsum / (double)pre;
+            h.disc_mean = dsum / (double)PRE;
             hits[at] = h;
         }
     }
 }
 
 void launch_finalize(const View &vw, const SearchParams &sp, const Rec *recs, const uint8_t *lost,
-                     davis_hit *hits, Counters *ctr, cudaStream_t st) {
-    k_finalize<<<148 * 4, CONFIRM_WARPS * 32, 0, st>>>(vw, sp, recs, lost, hits, ctr);
+                     davis_hit *hits, unsigned int *per_stream, Counters *ctr, cudaStream_t st) {
+    k_finalize<<<148 * 4, CONFIRM_WARPS * 32, 0, st>>>(vw, sp, recs, lost, hits, per_stream, ctr);
+}
+
+// ---------------------------------------------------------------------------
+// Ordering.  The reference returns packets call by call, and inside a call in
+// its search order: ascending (index mod 14, index) (dsp.py:175-186).  The hit
+// list is brought into (stream, call, index mod 14, index) order on the device:
+// count per stream (k_finalize) -> exclusive scan -> bucket by stream -> rank
+// inside each bucket by counting smaller keys.  Keys are unique within a stream.
+// ---------------------------------------------------------------------------
+// start[0..n] = exclusive scan of count[0..n); fill[] is cleared.  One block.
+__global__ void __launch_bounds__(1024)
+k_scan_streams(const unsigned int *__restrict__ count, unsigned int *__restrict__ start,
+               unsigned int *__restrict__ fill, int n) {
+    __shared__ unsigned int warp_tot[32];
+    __shared__ unsigned int carry;
+    if (threadIdx.x == 0) carry = 0;
+    __syncthreads();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int base = 0; base < n; base += 1024) {
+        const int i = base + threadIdx.x;
+        const unsigned int x = i < n ? count[i] : 0u;
+        unsigned int incl = x;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const unsigned int y = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+            if (lane >= o) incl += y;
+        }
+        if (lane == 31) warp_tot[warp] = incl;
+        __syncthreads();
+        if (warp == 0) {
+            unsigned int t = warp_tot[lane], ti = t;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const unsigned int y = __shfl_up_sync(0xFFFFFFFFu, ti, o);
+                if (lane >= o) ti += y;
+            }
+            warp_tot[lane] = ti - t;                           // exclusive prefix of warp totals
+        }
+        __syncthreads();
+        const unsigned int c = carry;
+        if (i < n) {
+            start[i] = c + warp_tot[warp] + incl - x;
+            fill[i] = 0;
+        }
+        __syncthreads();
+        if (threadIdx.x == 1023) carry = c + warp_tot[warp] + incl;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) start[n] = carry;
+}
+
+__global__ void __launch_bounds__(256)
+k_bucket(const davis_hit *__restrict__ hits, const Counters *ctr, int stream0,
+         const unsigned int *__restrict__ start, unsigned int *__restrict__ fill,
+         unsigned int *__restrict__ bucket) {
+    const unsigned int n = ctr->n_hit;
+    for (unsigned int i = blockIdx.x * blockDim.x + threadIdx.x; i < n;
+         i += gridDim.x * blockDim.x) {
+        const unsigned int s = hits[i].stream - (unsigned int)stream0;
+        bucket[start[s] + atomicAdd(&fill[s], 1u)] = i;
+    }
+}
+
+__device__ __forceinline__ unsigned long long order_key(const davis_hit &h) {
+    return ((unsigned long long)h.call << 32) | ((unsigned long long)(h.index % SPS) << 24) |
+           (unsigned long long)(unsigned int)h.index;
+}
+
+constexpr int ORDER_THREADS = 128;
+constexpr int ORDER_TILE = 512;
+
+// one block per stream
+__global__ void __launch_bounds__(ORDER_THREADS)
+k_order(const davis_hit *__restrict__ hits, const unsigned int *__restrict__ start,
+        const unsigned int *__restrict__ bucket, davis_hit *__restrict__ out) {
+    __shared__ unsigned long long keys[ORDER_TILE];
+    const unsigned int base = start[blockIdx.x], n = start[blockIdx.x + 1] - base;
+    if (n == 0) return;
+    for (unsigned int e0 = 0; e0 < n; e0 += ORDER_THREADS) {
+        const unsigned int e = e0 + threadIdx.x;
+        unsigned int src = 0, rank = 0;
+        unsigned long long mine = 0;
+        if (e < n) {
+            src = bucket[base + e];
+            mine = order_key(hits[src]);
+        }
+        for (unsigned int t0 = 0; t0 < n; t0 += ORDER_TILE) {
+            const unsigned int tn = min((unsigned int)ORDER_TILE, n - t0);
+            __syncthreads();
+            for (unsigned int j = threadIdx.x; j < tn; j += ORDER_THREADS)
+                keys[j] = order_key(hits[bucket[base + t0 + j]]);
+            __syncthreads();
+            if (e < n)
+                for (unsigned int j = 0; j < tn; j++) rank += keys[j] < mine;
+        }
+        if (e < n) out[base + rank] = hits[src];
+    }
+}
+
+void launch_order(const davis_hit *tmp, const Counters *ctr, int stream0, int n_streams,
+                  unsigned int *per_stream, unsigned int *start, unsigned int *fill,
+                  unsigned int *bucket, davis_hit *out, cudaStream_t st) {
+    k_scan_streams<<<1, 1024, 0, st>>>(per_stream, start, fill, n_streams);
+    k_bucket<<<148 * 2, 256, 0, st>>>(tmp, ctr, stream0, start, fill, bucket);
+    k_order<<<n_streams, ORDER_THREADS, 0, st>>>(tmp, start, bucket, out);
 }
 
 // ---------------------------------------------------------------------------
@@ -404,7 +525,7 @@ __global__ void k_exact_disc(View vw, int stream, int v0, int n, double *out) {
     __shared__ double lut[256];
     stage_lut(lut, vw.lut);
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) out[i] = exact_disc(lut, vw, stream, v0 + i);
+    if (i < n) out[i] = exact_disc(lut, GlobalSrc(vw, stream), v0 + i);
 }
 
 void launch_exact_disc(const View &vw, int stream, int v0, int n, double *out, cudaStream_t st) {

@@ -102,6 +102,7 @@ class BatchDemodulator:
             check(rc)
         self._keepalive = None
         self._last_blocks = 0
+        self._hit_guess = 256
         self.calls_done = 0
 
     # -- lifetime ---------------------------------------------------------
@@ -170,11 +171,12 @@ class BatchDemodulator:
 
     def fetch(self) -> np.ndarray:
         n = C.c_size_t(0)
-        out = np.empty(256, dtype=HIT_DTYPE)
+        out = np.empty(self._hit_guess, dtype=HIT_DTYPE)
         rc = self._L.davis_fetch_hits(self._h, out.ctypes.data, out.size, C.byref(n))
         if rc == _lib.E_OVERFLOW and n.value > out.size:
             out = np.empty(n.value, dtype=HIT_DTYPE)
             rc = self._L.davis_fetch_hits(self._h, out.ctypes.data, out.size, C.byref(n))
+        self._hit_guess = max(256, int(n.value * 1.25) + 16)
         self._keepalive = None
         check(rc, self._h)
         self.calls_done += self._last_blocks
