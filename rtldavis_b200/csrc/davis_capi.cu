@@ -33,7 +33,7 @@ struct Stage {
     unsigned int *per_stream = nullptr;  size_t per_stream_cap = 0;   // count | start | fill
     Counters *ctr = nullptr;
     int last_group = -1;
-    int tiles_alloc = 0;
+    int tiles = 0, words_alloc = 0;
 };
 
 struct Group {
@@ -67,7 +67,6 @@ struct davis_handle {
     bool have_results = false;
     std::vector<davis_hit> results;
     davis_stats stats{};
-    int variant = 0;
     std::string err;
 };
 
@@ -101,16 +100,15 @@ int grow(davis_handle *h, T **p, size_t *have, size_t want) {
     return DAVIS_OK;
 }
 
-int tiles_needed(int v_len) { return (v_len + TILE - 1) / TILE; }
+int tiles_needed(int v_len) { return (v_len + TILE_SAMPLES - 1) / TILE_SAMPLES; }
 
 int prepare_stage(davis_handle *h, Stage &st, int ns, int n_blocks, size_t staging_bytes,
                   size_t rec_cap) {
     const int v_len = h->n_carry + n_blocks * h->B;
-    int tiles = tiles_needed(v_len) + 1;                       // +1: the search reads tile j+1
-    tiles = (tiles + DEMOD_WARPS - 1) / DEMOD_WARPS * DEMOD_WARPS;
-    st.tiles_alloc = tiles;
+    st.tiles = tiles_needed(v_len);
+    st.words_alloc = st.tiles * TILE_WORDS + SEARCH_AHEAD;
     int rc;
-    if ((rc = grow(h, &st.planes, &st.planes_words, (size_t)ns * tiles * PLANE_WORDS))) return rc;
+    if ((rc = grow(h, &st.planes, &st.planes_words, (size_t)ns * st.words_alloc))) return rc;
     if (staging_bytes && (rc = grow(h, &st.staging, &st.staging_bytes, staging_bytes))) return rc;
     // expected near-matches: 17/65536 per sample position; allow 4x plus slack
     const double positions = (double)ns * ((double)n_blocks + h->W) * h->B;
@@ -175,8 +173,8 @@ int run_group(davis_handle *h, Stage &stage, Group &g, int gi, const uint8_t *de
     sp.pat_rev = h->pat_rev;
     sp.v_lo = HALO;
     sp.v_hi = HALO + n_blocks * h->B;
-    sp.tiles = sp.v_hi / TILE + 1;
-    sp.tiles_alloc = stage.tiles_alloc;
+    sp.words = sp.v_hi / LANE_SAMPLES + 1;
+    sp.words_alloc = stage.words_alloc;
     sp.n_streams = g.ns;
     sp.cand_cap = stage.cand_cap;
     sp.conf_cap = stage.conf_cap;
@@ -187,7 +185,7 @@ int run_group(davis_handle *h, Stage &stage, Group &g, int gi, const uint8_t *de
     CU(cudaMemsetAsync(stage.tbl, 0xFF, stage.tbl_size * sizeof(uint32_t), st));
     CU(cudaMemsetAsync(stage.lost, 0, g.hit_cap, st));
     CU(cudaEventRecord(g.ev[0], st));
-    launch_demod(vw, stage.planes, g.ns, stage.tiles_alloc, h->variant, nullptr, 0, st);
+    launch_demod(vw, stage.planes, g.ns, stage.tiles, stage.words_alloc, nullptr, 0, st);
     CU(cudaEventRecord(g.ev[1], st));
     launch_search(stage.planes, sp, stage.cand, stage.ctr, st);
     CU(cudaEventRecord(g.ev[2], st));
@@ -256,8 +254,6 @@ int davis_create(const davis_cfg *cfg, int n_streams, int device, davis_handle *
     for (int i = 0; i < PRE_SYMS; i++)                           // symbol 0 is the MSB
         h->pat_rev |= ((cfg->preamble >> (PRE_SYMS - 1 - i)) & 1u) << i;
     h->h_blocks_done.assign(n_streams, 0);
-    const char *var = getenv("DAVIS_DEMOD_VARIANT");
-    h->variant = var ? atoi(var) : 0;
 
     auto bail = [&](int rc) { davis_destroy(h); return rc; };
     if (cudaSetDevice(device) != cudaSuccess) return bail(DAVIS_E_CUDA);
@@ -517,13 +513,13 @@ int davis_debug_bits(davis_handle *h, int stream, uint8_t *out, size_t cap, int6
         *n = count;
         *first = (h->h_blocks_done[stream] - h->queued_blocks) * (int64_t)h->B - h->n_carry + HALO;
         if (count > cap) return fail(h, DAVIS_E_OVERFLOW, "bit buffer too small");
-        std::vector<uint32_t> words((size_t)st.tiles_alloc * PLANE_WORDS);
+        std::vector<uint32_t> words((size_t)st.words_alloc);
         CU(cudaMemcpy(words.data(),
-                      st.planes + (size_t)(stream - g.s0) * st.tiles_alloc * PLANE_WORDS,
+                      st.planes + (size_t)(stream - g.s0) * st.words_alloc,
                       words.size() * 4, cudaMemcpyDeviceToHost));
         for (size_t i = 0; i < count; i++) {
-            const size_t v = i + HALO, sym = v / SPS, ph = v % SPS;
-            out[i] = (uint8_t)((words[(sym >> 5) * PLANE_WORDS + ph] >> (sym & 31)) & 1u);
+            const size_t v = i + HALO;
+            out[i] = (uint8_t)((words[v / LANE_SAMPLES] >> (v % LANE_SAMPLES)) & 1u);
         }
         return DAVIS_OK;
     }
@@ -572,17 +568,17 @@ int davis_debug_disc32(davis_handle *h, int stream, float *out, size_t cap) {
     debug_view(h, &vw);
     vw.carry += (size_t)stream * h->carry_stride;
     vw.blocks_done += stream;
-    int tiles = tiles_needed(h->n_keep) + 1;
-    tiles = (tiles + DEMOD_WARPS - 1) / DEMOD_WARPS * DEMOD_WARPS;
+    const int tiles = tiles_needed(h->n_keep);
+    const int words_alloc = tiles * TILE_WORDS;
     uint32_t *planes = nullptr;
     float *d = nullptr;
-    const size_t n_disc = (size_t)tiles * TILE;
-    CU(cudaMalloc((void **)&planes, sizeof(uint32_t) * tiles * PLANE_WORDS));
+    const size_t n_disc = (size_t)tiles * TILE_SAMPLES;
+    CU(cudaMalloc((void **)&planes, sizeof(uint32_t) * words_alloc));
     if (cudaMalloc((void **)&d, sizeof(float) * n_disc) != cudaSuccess) {
         cudaFree(planes);
         return fail(h, DAVIS_E_NOMEM, "cudaMalloc");
     }
-    launch_demod(vw, planes, 1, tiles, 0, d, n_disc, 0);
+    launch_demod(vw, planes, 1, tiles, words_alloc, d, n_disc, 0);
     cudaError_t e = cudaMemcpy(out, d + (h->n_keep - 2 * h->B), sizeof(float) * 2 * h->B,
                                cudaMemcpyDeviceToHost);
     cudaFree(planes);

@@ -19,8 +19,11 @@ constexpr int PRE_SYMS = 16;     // sync symbols
 constexpr int PKT_SYMS = 80;     // sliced symbols
 constexpr int PKT_BYTES = 10;
 constexpr int HALO = 16;         // extra history samples kept in front of the carried blocks
-constexpr int TILE = 32 * SPS;   // samples decided by one warp pass: 32 symbols
-constexpr int PLANE_WORDS = 16;  // words stored per tile (14 phase planes + 2 pad)
+// decision bitmap: word w of a stream holds samples [28w, 28w+28), bit i = sample 28w+i
+constexpr int LANE_SAMPLES = 2 * SPS;                    // 28 decisions per 32-bit word
+constexpr int TILE_WORDS = 256;                          // words per demod tile (one per thread)
+constexpr int TILE_SAMPLES = TILE_WORDS * LANE_SAMPLES;  // 7168
+constexpr int SEARCH_AHEAD = 9;                          // words read beyond a position's own
 
 // fir9 taps, src/rtldavis/dsp.py:56-69
 #define DAVIS_C0 0.017682261285

@@ -42,16 +42,17 @@ struct Counters {
 struct SearchParams {
     uint32_t pat_rev;          // sync word with symbol 0 in bit 0
     int v_lo, v_hi;            // inclusive range of reportable positions
-    int tiles;                 // tiles per stream that hold decided bits
-    int tiles_alloc;           // tiles per stream in the plane buffer
+    int words;                 // words per stream that hold reportable positions
+    int words_alloc;           // words per stream in the bitmap
     int n_streams;
     unsigned int cand_cap, conf_cap, hit_cap;
     unsigned int tbl_mask;     // dedupe hash table size - 1 (power of two)
 };
 
 constexpr int DEMOD_WARPS = 8;
+constexpr int DEMOD_CTAS_PER_SM = 3;
 
-void launch_demod(const View &vw, uint32_t *planes, int n_streams, int tiles_alloc, int variant,
+void launch_demod(const View &vw, uint32_t *words, int n_streams, int tiles, int words_alloc,
                   float *disc_out, size_t disc_stride, cudaStream_t st);
 void launch_search(const uint32_t *planes, const SearchParams &sp, Cand *cand, Counters *ctr,
                    cudaStream_t st);

@@ -10,17 +10,22 @@
 namespace davis {
 
 // ---------------------------------------------------------------------------
-// k_search: one thread per (stream, tile, phase) word of 32 symbols.
-// A position is a candidate when the 16 symbols starting there differ from the
-// sync word in at most one symbol.  By pigeonhole such a window matches the
-// first or the second half of the word exactly, so the word-parallel part only
-// computes two 8-literal AND chains; the rare survivors are checked with popc.
-// The one-symbol slack exists because the planes come from fp32 arithmetic: a
+// k_search: one thread per bitmap word (28 sample positions).
+// The preamble's symbol i of a position v = 28w + b sits at sample v + 14i, i.e.
+// for even i = 2m at bit b of word w+m, and for odd i = 2m+1 at bit b of the
+// "half-step" word H[m] = (W[w+m] >> 14) | (W[w+m+1] << 14).  So the sixteen
+// comparisons of all 28 positions are sixteen bitwise ops on whole words.
+// A position is a candidate when its 16 symbols differ from the sync word in at
+// most one symbol.  By pigeonhole such a window matches the even-numbered or the
+// odd-numbered symbols exactly, so the word-parallel part only computes two
+// 8-literal AND chains; the rare survivors are checked with popc.
+// The one-symbol slack exists because the bitmap comes from fp32 arithmetic: a
 // true match (in the reference's float64) with one marginal fp32 sign must not
 // be lost.  k_precheck settles such positions in fp64.
 // ---------------------------------------------------------------------------
 constexpr int SEARCH_THREADS = 256;
 constexpr int STAGE = 128;   // per-block staging slots for found candidates
+constexpr uint32_t MASK28 = 0x0FFFFFFFu;
 
 template <typename T>
 __device__ __forceinline__ void block_flush(T *stage, int n_staged, T *out, unsigned int *counter,
@@ -38,7 +43,7 @@ __device__ __forceinline__ void block_flush(T *stage, int n_staged, T *out, unsi
 }
 
 __global__ void __launch_bounds__(SEARCH_THREADS)
-k_search(const uint32_t *__restrict__ planes, SearchParams sp, Cand *__restrict__ cand,
+k_search(const uint32_t *__restrict__ words, SearchParams sp, Cand *__restrict__ cand,
          Counters *ctr) {
     __shared__ Cand stage[STAGE];
     __shared__ int n_stage;
@@ -46,30 +51,33 @@ k_search(const uint32_t *__restrict__ planes, SearchParams sp, Cand *__restrict_
     if (threadIdx.x == 0) n_stage = 0;
     __syncthreads();
 
-    const long long word = (long long)blockIdx.x * SEARCH_THREADS + threadIdx.x;
-    const int p = (int)(word & (PLANE_WORDS - 1));
-    const long long tile_lin = word >> 4;
-    const int s = (int)(tile_lin / sp.tiles);
-    const int j = (int)(tile_lin - (long long)s * sp.tiles);
+    const long long id = (long long)blockIdx.x * SEARCH_THREADS + threadIdx.x;
+    const int s = (int)(id / sp.words);
+    const int w = (int)(id - (long long)s * sp.words);
 
-    if (s < sp.n_streams && p < SPS) {
-        const uint32_t *base = planes + ((size_t)s * sp.tiles_alloc + j) * PLANE_WORDS + p;
-        const uint32_t w0 = __ldg(base), w1 = __ldg(base + PLANE_WORDS);
-        uint32_t lo = 0xFFFFFFFFu, hi = 0xFFFFFFFFu;
+    if (s < sp.n_streams) {
+        const uint32_t *base = words + (size_t)s * sp.words_alloc + w;
+        uint32_t e[9], h[8];
 #pragma unroll
-        for (int i = 0; i < 8; i++) {
-            const uint32_t x = __funnelshift_r(w0, w1, i);
-            const uint32_t y = __funnelshift_r(w0, w1, i + 8);
-            lo &= ((sp.pat_rev >> i) & 1u) ? x : ~x;
-            hi &= ((sp.pat_rev >> (i + 8)) & 1u) ? y : ~y;
+        for (int m = 0; m < 9; m++) e[m] = __ldg(base + m);
+#pragma unroll
+        for (int m = 0; m < 8; m++) h[m] = ((e[m] >> SPS) | (e[m + 1] << SPS)) & MASK28;
+        uint32_t even = MASK28, odd = MASK28;
+#pragma unroll
+        for (int m = 0; m < 8; m++) {
+            even &= ((sp.pat_rev >> (2 * m)) & 1u) ? e[m] : ~e[m];
+            odd &= ((sp.pat_rev >> (2 * m + 1)) & 1u) ? h[m] : ~h[m];
         }
-        uint32_t m = lo | hi;
-        while (m) {
-            const int l = __ffs(m) - 1;
-            m &= m - 1;
-            const int v = SPS * (32 * j + l) + p;
+        uint32_t hit = even | odd;
+        while (hit) {
+            const int b = __ffs(hit) - 1;
+            hit &= hit - 1;
+            const int v = LANE_SAMPLES * w + b;
             if (v < sp.v_lo || v > sp.v_hi) continue;
-            const uint32_t win = __funnelshift_r(w0, w1, l) & 0xFFFFu;
+            uint32_t win = 0;
+#pragma unroll
+            for (int i = 0; i < PRE_SYMS; i++)
+                win |= ((((i & 1) ? h[i >> 1] : e[i >> 1]) >> b) & 1u) << i;
             const uint32_t diff = win ^ sp.pat_rev;
             if (__popc(diff) > 1) continue;
             Cand c;
@@ -91,11 +99,11 @@ k_search(const uint32_t *__restrict__ planes, SearchParams sp, Cand *__restrict_
                 &s_base);
 }
 
-void launch_search(const uint32_t *planes, const SearchParams &sp, Cand *cand, Counters *ctr,
+void launch_search(const uint32_t *words, const SearchParams &sp, Cand *cand, Counters *ctr,
                    cudaStream_t st) {
-    const long long words = (long long)sp.n_streams * sp.tiles * PLANE_WORDS;
-    const unsigned grid = (unsigned)((words + SEARCH_THREADS - 1) / SEARCH_THREADS);
-    if (grid) k_search<<<grid, SEARCH_THREADS, 0, st>>>(planes, sp, cand, ctr);
+    const long long total = (long long)sp.n_streams * sp.words;
+    const unsigned grid = (unsigned)((total + SEARCH_THREADS - 1) / SEARCH_THREADS);
+    if (grid) k_search<<<grid, SEARCH_THREADS, 0, st>>>(words, sp, cand, ctr);
 }
 
 // ---------------------------------------------------------------------------
@@ -240,9 +248,8 @@ k_confirm(View vw, SearchParams sp, const uint32_t *__restrict__ planes,
             if (i < PKT_SYMS) {
                 const int v = c.v + SPS * i;
                 bit = exact_bit(lut, src, v);
-                const int sym = v / SPS, ph = v - sym * SPS;
-                fast = (planes[((size_t)s * sp.tiles_alloc + (sym >> 5)) * PLANE_WORDS + ph] >>
-                        (sym & 31)) & 1u;
+                const int wd = v / LANE_SAMPLES;
+                fast = (planes[(size_t)s * sp.words_alloc + wd] >> (v - wd * LANE_SAMPLES)) & 1u;
             }
             m[part] = __ballot_sync(0xFFFFFFFFu, bit);
             disagree |= __ballot_sync(0xFFFFFFFFu, bit != fast);
