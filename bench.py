@@ -261,7 +261,7 @@ def run_graft(a):
 
     def step_device():
         bd.submit(dev, cuda_stream=sptr)
-        return bd.fetch()
+        return bd.fetch(copy=False)
 
     # ---- device-resident: `value` ----
     hits = None
@@ -320,13 +320,13 @@ def run_graft(a):
         bd2 = dsp.BatchDemodulator(cfg, a.streams, device=local, max_blocks=a.blocks)
         for _ in range(max(1, min(a.warmup, 2))):
             bd2.submit(host_np)
-            h2 = bd2.fetch()
+            h2 = bd2.fetch(copy=False)
         barrier()
         t0 = time.perf_counter()
         h2d = d2h = 0
         for _ in range(a.steps):
             bd2.submit(host_np)
-            h2 = bd2.fetch()
+            h2 = bd2.fetch(copy=False)
             st2 = bd2.stats()
             h2d, d2h = int(st2.h2d_bytes), int(st2.d2h_bytes)
         torch.cuda.synchronize()

@@ -136,6 +136,10 @@ DAVIS_API int davis_demod_c64(davis_handle *h, const float *iq, size_t samples_p
  * called again with a larger buffer. */
 DAVIS_API int davis_fetch_hits(davis_handle *h, davis_hit *out, size_t cap, size_t *n);
 
+/* Same, without the copy: *out points at the handle's own (pinned) result buffer,
+ * valid until the next davis_demod_*, davis_reset or davis_destroy on the handle. */
+DAVIS_API int davis_fetch_hits_view(davis_handle *h, const davis_hit **out, size_t *n);
+
 DAVIS_API int davis_get_stats(davis_handle *h, davis_stats *out);
 
 /* Verification taps (not on the product path).

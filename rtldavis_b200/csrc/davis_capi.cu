@@ -38,7 +38,7 @@ struct Stage {
 
 struct Group {
     int stage = 0, s0 = 0, ns = 0;
-    size_t hit_off = 0;  unsigned int hit_cap = 0;
+    size_t hit_off = 0;  unsigned int hit_cap = 0, n_hit = 0;
     cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
 };
 
@@ -65,7 +65,8 @@ struct davis_handle {
     bool queued = false;
     int queued_blocks = 0;
     bool have_results = false;
-    std::vector<davis_hit> results;
+    size_t n_results = 0;
+    davis_hit *h_hits = nullptr;  size_t h_hits_cap = 0;       // pinned; the fetched packets
     davis_stats stats{};
     std::string err;
 };
@@ -304,6 +305,7 @@ int davis_destroy(davis_handle *h) {
     if (h->d_lut) cudaFree(h->d_lut);
     if (h->d_hits) cudaFree(h->d_hits);
     if (h->h_ctr) cudaFreeHost(h->h_ctr);
+    if (h->h_hits) cudaFreeHost(h->h_hits);
     delete h;
     return DAVIS_OK;
 }
@@ -421,13 +423,13 @@ int davis_demod_c64(davis_handle *h, const float *, size_t, size_t, int, void *)
     return fail(h, DAVIS_E_INVAL, "complex64 input is not implemented yet");
 }
 
-int davis_fetch_hits(davis_handle *h, davis_hit *out, size_t cap, size_t *n) {
-    if (!h || !n) return DAVIS_E_INVAL;
+// Wait for the queued call and bring its packets into the pinned result buffer.
+static int complete_call(davis_handle *h) {
     CU(cudaSetDevice(h->device));
     if (h->queued) {
-        h->results.clear();
+        h->n_results = 0;
         float demod = 0, search = 0, finish = 0;
-        double t_wait = 0, t_copy = 0;
+        double t_wait = 0;
         for (size_t gi = 0; gi < h->groups.size(); gi++) {
             Group &g = h->groups[gi];
             const double t0 = now_ms();
@@ -449,15 +451,8 @@ int davis_fetch_hits(davis_handle *h, davis_hit *out, size_t cap, size_t *n) {
                          c.overflow, c.n_cand, c.n_conf, c.n_rec);
                 return fail(h, DAVIS_E_OVERFLOW, msg);
             }
-            const size_t at = h->results.size();
-            h->results.resize(at + c.n_hit);
-            if (c.n_hit) {
-                const double t1 = now_ms();
-                CU(cudaMemcpy(h->results.data() + at, h->d_hits + g.hit_off,
-                              sizeof(davis_hit) * c.n_hit, cudaMemcpyDeviceToHost));
-                t_copy += now_ms() - t1;
-                h->stats.d2h_bytes += sizeof(davis_hit) * c.n_hit;
-            }
+            g.n_hit = c.n_hit;
+            h->n_results += c.n_hit;
             h->stats.d2h_bytes += sizeof(Counters);
         }
         h->stats.demod_ms = demod;
@@ -477,16 +472,53 @@ int davis_fetch_hits(davis_handle *h, davis_hit *out, size_t cap, size_t *n) {
         // (dsp.py:203-205) and delivered every group in (stream, call, index mod 14,
         // index) order (dsp.py:175-186); groups hold ascending stream ranges.
         h->stats.host_wait_ms = (float)t_wait;
-        h->stats.host_copy_ms = (float)t_copy;
         h->stats.host_sort_ms = 0.0f;
+        // one DMA per group into the handle's pinned result buffer
+        const double t1 = now_ms();
+        if (h->h_hits_cap < h->n_results) {
+            if (h->h_hits) CU(cudaFreeHost(h->h_hits));
+            h->h_hits = nullptr; h->h_hits_cap = 0;
+            const size_t want = h->n_results + h->n_results / 4 + 1024;
+            CU(cudaHostAlloc((void **)&h->h_hits, want * sizeof(davis_hit), cudaHostAllocDefault));
+            h->h_hits_cap = want;
+        }
+        size_t at = 0;
+        for (const Group &g : h->groups) {
+            if (!g.n_hit) continue;
+            CU(cudaMemcpyAsync(h->h_hits + at, h->d_hits + g.hit_off, sizeof(davis_hit) * g.n_hit,
+                               cudaMemcpyDeviceToHost, h->stages[g.stage].st));
+            at += g.n_hit;
+        }
+        for (auto &st : h->stages) if (st.st) CU(cudaStreamSynchronize(st.st));
+        h->stats.host_copy_ms = (float)(now_ms() - t1);
+        h->stats.d2h_bytes += sizeof(davis_hit) * at;
         h->queued = false;
         h->have_results = true;
     } else if (!h->have_results) {
         return fail(h, DAVIS_E_STATE, "nothing queued");
     }
-    *n = h->results.size();
+    return DAVIS_OK;
+}
+
+int davis_fetch_hits(davis_handle *h, davis_hit *out, size_t cap, size_t *n) {
+    if (!h || !n) return DAVIS_E_INVAL;
+    const int rc = complete_call(h);
+    if (rc) return rc;
+    *n = h->n_results;
     if (*n > cap) return fail(h, DAVIS_E_OVERFLOW, "caller buffer smaller than the packet count");
-    if (*n) memcpy(out, h->results.data(), sizeof(davis_hit) * *n);
+    if (*n && !out) return fail(h, DAVIS_E_INVAL, "null output buffer");
+    if (*n) memcpy(out, h->h_hits, sizeof(davis_hit) * *n);
+    return DAVIS_OK;
+}
+
+int davis_fetch_hits_view(davis_handle *h, const davis_hit **out, size_t *n) {
+    if (!h || !out || !n) return DAVIS_E_INVAL;
+    *out = nullptr;
+    *n = 0;
+    const int rc = complete_call(h);
+    if (rc) return rc;
+    *out = h->n_results ? h->h_hits : nullptr;
+    *n = h->n_results;
     return DAVIS_OK;
 }
 

@@ -23,7 +23,7 @@ constexpr int HALO = 16;         // extra history samples kept in front of the c
 constexpr int LANE_SAMPLES = 2 * SPS;                    // 28 decisions per 32-bit word
 constexpr int TILE_WORDS = 256;                          // words per demod tile (one per thread)
 constexpr int TILE_SAMPLES = TILE_WORDS * LANE_SAMPLES;  // 7168
-constexpr int SEARCH_AHEAD = 9;                          // words read beyond a position's own
+constexpr int SEARCH_AHEAD = 12;                         // words the search may read past the last tile (keeps rows 16-byte aligned)
 
 // fir9 taps, src/rtldavis/dsp.py:56-69
 #define DAVIS_C0 0.017682261285
@@ -162,6 +162,28 @@ __device__ __forceinline__ Cplx exact_filtered(const double *lut, const Src &src
         f.im = __dadd_rn(f.im, __dmul_rn(taps[m], r.im));
     }
     return f;
+}
+
+// F[v_first + k] for k = 0..NF-1 from the NF + 8 samples they share (register
+// sliding window); every sum runs m = 0..8 exactly as exact_filtered does.
+template <int NF, class Src>
+__device__ __forceinline__ void exact_filtered_run(const double *lut, const Src &src, int v_first,
+                                                   Cplx (&F)[NF]) {
+    const double taps[9] = {DAVIS_C0, DAVIS_C1, DAVIS_C2, DAVIS_C3, DAVIS_C4,
+                            DAVIS_C3, DAVIS_C2, DAVIS_C1, DAVIS_C0};
+    Cplx r[NF + 8];
+#pragma unroll
+    for (int i = 0; i < NF + 8; i++) r[i] = exact_rotated(lut, src, v_first - 9 + i);
+#pragma unroll
+    for (int k = 0; k < NF; k++) {
+        Cplx f{0.0, 0.0};
+#pragma unroll
+        for (int m = 0; m < 9; m++) {
+            f.re = __dadd_rn(f.re, __dmul_rn(taps[m], r[k + m].re));
+            f.im = __dadd_rn(f.im, __dmul_rn(taps[m], r[k + m].im));
+        }
+        F[k] = f;
+    }
 }
 
 // numerator of D[g]: Im a * Re b - Re a * Im b,  a = F[g-1], b = F[g]

@@ -16,9 +16,9 @@ namespace davis {
 // "half-step" word H[m] = (W[w+m] >> 14) | (W[w+m+1] << 14).  So the sixteen
 // comparisons of all 28 positions are sixteen bitwise ops on whole words.
 // A position is a candidate when its 16 symbols differ from the sync word in at
-// most one symbol.  By pigeonhole such a window matches the even-numbered or the
-// odd-numbered symbols exactly, so the word-parallel part only computes two
-// 8-literal AND chains; the rare survivors are checked with popc.
+// most one symbol; a two-bit saturating mismatch counter is kept bit-sliced (two
+// words) so that test, too, is word-parallel and only true candidates (17 in
+// 65536 positions of noise) reach the scalar code.
 // The one-symbol slack exists because the bitmap comes from fp32 arithmetic: a
 // true match (in the reference's float64) with one marginal fp32 sign must not
 // be lost.  k_precheck settles such positions in fp64.
@@ -42,6 +42,8 @@ __device__ __forceinline__ void block_flush(T *stage, int n_staged, T *out, unsi
     }
 }
 
+constexpr int SEARCH_WORDS = 4;      // bitmap words per thread (one 16-byte load + 8 words of lookahead)
+
 __global__ void __launch_bounds__(SEARCH_THREADS)
 k_search(const uint32_t *__restrict__ words, SearchParams sp, Cand *__restrict__ cand,
          Counters *ctr) {
@@ -51,46 +53,63 @@ k_search(const uint32_t *__restrict__ words, SearchParams sp, Cand *__restrict__
     if (threadIdx.x == 0) n_stage = 0;
     __syncthreads();
 
+    const int quads = (sp.words + SEARCH_WORDS - 1) / SEARCH_WORDS;
     const long long id = (long long)blockIdx.x * SEARCH_THREADS + threadIdx.x;
-    const int s = (int)(id / sp.words);
-    const int w = (int)(id - (long long)s * sp.words);
+    const int s = (int)(id / quads);
+    const int w0 = (int)(id - (long long)s * quads) * SEARCH_WORDS;
 
     if (s < sp.n_streams) {
-        const uint32_t *base = words + (size_t)s * sp.words_alloc + w;
-        uint32_t e[9], h[8];
+        // literal masks of the sync word: symbol i must be 1 -> 0, must be 0 -> ~0
+        uint32_t inv[PRE_SYMS];
 #pragma unroll
-        for (int m = 0; m < 9; m++) e[m] = __ldg(base + m);
+        for (int i = 0; i < PRE_SYMS; i++) inv[i] = ((sp.pat_rev >> i) & 1u) ? 0u : 0xFFFFFFFFu;
+
+        const uint4 *base = reinterpret_cast<const uint4 *>(words + (size_t)s * sp.words_alloc + w0);
+        uint32_t e[SEARCH_WORDS + 8], h[SEARCH_WORDS + 7];
 #pragma unroll
-        for (int m = 0; m < 8; m++) h[m] = ((e[m] >> SPS) | (e[m + 1] << SPS)) & MASK28;
-        uint32_t even = MASK28, odd = MASK28;
-#pragma unroll
-        for (int m = 0; m < 8; m++) {
-            even &= ((sp.pat_rev >> (2 * m)) & 1u) ? e[m] : ~e[m];
-            odd &= ((sp.pat_rev >> (2 * m + 1)) & 1u) ? h[m] : ~h[m];
+        for (int k = 0; k < (SEARCH_WORDS + 8) / 4; k++) {
+            const uint4 t = __ldg(base + k);
+            e[4 * k] = t.x; e[4 * k + 1] = t.y; e[4 * k + 2] = t.z; e[4 * k + 3] = t.w;
         }
-        uint32_t hit = even | odd;
-        while (hit) {
-            const int b = __ffs(hit) - 1;
-            hit &= hit - 1;
-            const int v = LANE_SAMPLES * w + b;
-            if (v < sp.v_lo || v > sp.v_hi) continue;
-            uint32_t win = 0;
 #pragma unroll
-            for (int i = 0; i < PRE_SYMS; i++)
-                win |= ((((i & 1) ? h[i >> 1] : e[i >> 1]) >> b) & 1u) << i;
-            const uint32_t diff = win ^ sp.pat_rev;
-            if (__popc(diff) > 1) continue;
-            Cand c;
-            c.stream = (uint32_t)s;
-            c.v = v;
-            c.miss = diff ? __ffs(diff) - 1 : -1;
-            c.pad = 0;
-            const int slot = atomicAdd(&n_stage, 1);
-            if (slot < STAGE) stage[slot] = c;
-            else {                                    // staging full: append directly
-                const unsigned int at = atomicAdd(&ctr->n_cand, 1u);
-                if (at < sp.cand_cap) cand[at] = c;
-                else atomicOr(&ctr->overflow, 1u);
+        for (int m = 0; m < SEARCH_WORDS + 7; m++) h[m] = (e[m] >> SPS) | (e[m + 1] << SPS);
+#pragma unroll
+        for (int k = 0; k < SEARCH_WORDS; k++) {
+            // word-parallel mismatch counter saturating at two: c1 = "some symbol
+            // differs", c2 = "two or more differ", for all 28 positions at once
+            uint32_t c1 = 0, c2 = 0;
+#pragma unroll
+            for (int m = 0; m < 8; m++) {
+                const uint32_t de = ~(e[k + m] ^ inv[2 * m]);
+                c2 |= c1 & de;
+                c1 |= de;
+                const uint32_t dh = ~(h[k + m] ^ inv[2 * m + 1]);
+                c2 |= c1 & dh;
+                c1 |= dh;
+            }
+            uint32_t hit = ~c2 & MASK28;
+            while (hit) {
+                const int b = __ffs(hit) - 1;
+                hit &= hit - 1;
+                const int v = LANE_SAMPLES * (w0 + k) + b;
+                if (v < sp.v_lo || v > sp.v_hi) continue;
+                uint32_t win = 0;
+#pragma unroll
+                for (int i = 0; i < PRE_SYMS; i++)
+                    win |= ((((i & 1) ? h[k + (i >> 1)] : e[k + (i >> 1)]) >> b) & 1u) << i;
+                const uint32_t diff = win ^ sp.pat_rev;           // at most one bit set
+                Cand c;
+                c.stream = (uint32_t)s;
+                c.v = v;
+                c.miss = diff ? __ffs(diff) - 1 : -1;
+                c.pad = 0;
+                const int slot = atomicAdd(&n_stage, 1);
+                if (slot < STAGE) stage[slot] = c;
+                else {                                    // staging full: append directly
+                    const unsigned int at = atomicAdd(&ctr->n_cand, 1u);
+                    if (at < sp.cand_cap) cand[at] = c;
+                    else atomicOr(&ctr->overflow, 1u);
+                }
             }
         }
     }
@@ -101,7 +120,7 @@ k_search(const uint32_t *__restrict__ words, SearchParams sp, Cand *__restrict__
 
 void launch_search(const uint32_t *words, const SearchParams &sp, Cand *cand, Counters *ctr,
                    cudaStream_t st) {
-    const long long total = (long long)sp.n_streams * sp.words;
+    const long long total = (long long)sp.n_streams * ((sp.words + SEARCH_WORDS - 1) / SEARCH_WORDS);
     const unsigned grid = (unsigned)((total + SEARCH_THREADS - 1) / SEARCH_THREADS);
     if (grid) k_search<<<grid, SEARCH_THREADS, 0, st>>>(words, sp, cand, ctr);
 }
@@ -307,13 +326,32 @@ void launch_confirm(const View &vw, const SearchParams &sp, const uint32_t *plan
 // one-block `filtered` buffer indexed by two-block window positions) and the
 // discriminator mean Parser.parse takes (protocol.py:304-310), all in fp64.
 // ---------------------------------------------------------------------------
-// sum of |F|^2 over V indices [v0, v1)
+// sum of |F|^2 over V indices [v0, v1), v1 - v0 <= 32 * FIN_CHUNK; lane l takes the
+// FIN_CHUNK consecutive positions starting at v0 + FIN_CHUNK * l
+constexpr int FIN_CHUNK = 7;                                   // 224 / 32
+
 __device__ double power_sum(const double *lut, const SpanSrc &src, int v0, int v1, int lane) {
     double acc = 0.0;
-    for (int v = v0 + lane; v < v1; v += 32) {
-        const Cplx f = exact_filtered(lut, src, v);
-        acc += f.re * f.re + f.im * f.im;
+    const int a = v0 + FIN_CHUNK * lane;
+    if (a < v1) {
+        Cplx F[FIN_CHUNK];
+        exact_filtered_run<FIN_CHUNK>(lut, src, a, F);
+#pragma unroll
+        for (int k = 0; k < FIN_CHUNK; k++)
+            if (a + k < v1) acc += F[k].re * F[k].re + F[k].im * F[k].im;
     }
+    return warp_sum(acc);
+}
+
+// sum of D[v] over [v0, v0 + 32 * FIN_CHUNK)
+__device__ double disc_sum(const double *lut, const SpanSrc &src, int v0, int lane) {
+    const int a = v0 + FIN_CHUNK * lane;
+    Cplx F[FIN_CHUNK + 1];
+    exact_filtered_run<FIN_CHUNK + 1>(lut, src, a - 1, F);
+    double acc = 0.0;
+#pragma unroll
+    for (int k = 0; k < FIN_CHUNK; k++)
+        acc += (src.g0 + a + k < 0) ? 0.0 : exact_disc_from(F[k], F[k + 1]);
     return warp_sum(acc);
 }
 
@@ -322,7 +360,8 @@ k_finalize(View vw, SearchParams sp, const Rec *__restrict__ recs,
            const uint8_t *__restrict__ lost, davis_hit *__restrict__ hits,
            unsigned int *__restrict__ per_stream, Counters *ctr) {
     constexpr int PRE = SPS * PRE_SYMS;                        // 224
-    constexpr int SPAN_P = 2 * PRE + 16, SPAN_D = PRE + 16;
+    constexpr int SPAN_P = 2 * PRE + 32, SPAN_D = PRE + 32;  // + FIR history + chunk overrun
+    static_assert(PRE == 32 * FIN_CHUNK, "one chunk per lane");
     __shared__ double lut[256];
     __shared__ uint4 mem_p[CONFIRM_WARPS][(2 * SPAN_P + 32 + 15) / 16];
     __shared__ uint4 mem_d[CONFIRM_WARPS][(2 * SPAN_D + 32 + 15) / 16];
@@ -355,9 +394,7 @@ k_finalize(View vw, SearchParams sp, const Rec *__restrict__ recs,
         const double sig = power_sum(lut, sp_p, f0 + q, f0 + s1, lane) / (double)(s1 - q);
         const double noise = q > n0 ? power_sum(lut, sp_p, f0 + n0, f0 + q, lane) / (double)(q - n0)
                                     : 1e-9;
-        double dsum = 0.0;
-        for (int t = lane; t < PRE; t += 32) dsum += exact_disc(lut, sp_d, d0 + t);
-        dsum = warp_sum(dsum);
+        const double dsum = disc_sum(lut, sp_d, d0, lane);
         if (lane == 0) {
             const unsigned int at = atomicAdd(&ctr->n_hit, 1u);   // <= n_rec <= hit_cap
             atomicAdd(&per_stream[s], 1u);

@@ -102,7 +102,6 @@ class BatchDemodulator:
             check(rc)
         self._keepalive = None
         self._last_blocks = 0
-        self._hit_guess = 256
         self.calls_done = 0
 
     # -- lifetime ---------------------------------------------------------
@@ -169,19 +168,21 @@ class BatchDemodulator:
         check(rc, self._h)
         self._last_blocks = n_blocks
 
-    def fetch(self) -> np.ndarray:
+    def fetch(self, copy: bool = True) -> np.ndarray:
+        """Packets of the submitted call.  With ``copy=False`` the array is a view of
+        the library's pinned result buffer, valid until the next submit()/reset()."""
         n = C.c_size_t(0)
-        out = np.empty(self._hit_guess, dtype=HIT_DTYPE)
-        rc = self._L.davis_fetch_hits(self._h, out.ctypes.data, out.size, C.byref(n))
-        if rc == _lib.E_OVERFLOW and n.value > out.size:
-            out = np.empty(n.value, dtype=HIT_DTYPE)
-            rc = self._L.davis_fetch_hits(self._h, out.ctypes.data, out.size, C.byref(n))
-        self._hit_guess = max(256, int(n.value * 1.25) + 16)
+        ptr = C.c_void_p()
+        rc = self._L.davis_fetch_hits_view(self._h, C.byref(ptr), C.byref(n))
         self._keepalive = None
         check(rc, self._h)
         self.calls_done += self._last_blocks
         self._last_blocks = 0
-        return out[: n.value]
+        if n.value == 0:
+            return np.empty(0, dtype=HIT_DTYPE)
+        buf = (C.c_char * (n.value * HIT_DTYPE.itemsize)).from_address(ptr.value)
+        view = np.frombuffer(buf, dtype=HIT_DTYPE, count=n.value)
+        return view.copy() if copy else view
 
     def stats(self) -> DavisStats:
         st = DavisStats()

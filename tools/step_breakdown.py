@@ -27,7 +27,7 @@ def main():
         t0 = time.perf_counter()
         bd.submit(dev)
         t1 = time.perf_counter()
-        hits = bd.fetch()
+        hits = bd.fetch(copy=False)
         t2 = time.perf_counter()
         st = bd.stats()
         if i >= 2:
