@@ -50,7 +50,7 @@ struct SearchParams {
 };
 
 constexpr int DEMOD_WARPS = 8;
-constexpr int DEMOD_CTAS_PER_SM = 3;
+constexpr int DEMOD_CTAS_PER_SM = 2;
 
 void launch_demod(const View &vw, uint32_t *words, int n_streams, int tiles, int words_alloc,
                   float *disc_out, size_t disc_stride, cudaStream_t st);
