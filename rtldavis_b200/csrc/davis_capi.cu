@@ -25,6 +25,10 @@ struct Stage {
     uint32_t *planes = nullptr;  size_t planes_words = 0;
     Cand *cand = nullptr;        unsigned int cand_cap = 0;
     Cand *conf = nullptr;        unsigned int conf_cap = 0;
+    uint32_t *marks = nullptr;   size_t marks_cap = 0;       // one bit per bitmap word group
+    uint2 *glist = nullptr;      size_t glist_cap = 0;       // groups queued for the fp64 pass
+    Fix *fixes = nullptr;
+    int mark_words = 0;
     Rec *recs = nullptr;         size_t recs_cap = 0;
     uint32_t *tbl = nullptr;     size_t tbl_size = 0;        // dedupe table, power of two
     uint8_t *lost = nullptr;     size_t lost_cap = 0;
@@ -120,6 +124,13 @@ int prepare_stage(davis_handle *h, Stage &st, int ns, int n_blocks, size_t stagi
     have = st.conf_cap;
     if ((rc = grow(h, &st.conf, &have, want / 2))) return rc;
     st.conf_cap = (unsigned int)have;
+    const int groups = (st.words_alloc + GROUP_WORDS - 1) / GROUP_WORDS;
+    st.mark_words = (groups + 31) / 32;
+    if ((rc = grow(h, &st.marks, &st.marks_cap, (size_t)ns * st.mark_words))) return rc;
+    const int per_pos = (SPS * (PKT_SYMS - 1)) / GROUP_SAMPLES + 2;        // groups one position touches
+    if ((rc = grow(h, &st.glist, &st.glist_cap,
+                   std::min((size_t)ns * groups, (size_t)st.conf_cap * per_pos)))) return rc;
+    if (!st.fixes) CU(cudaMalloc((void **)&st.fixes, sizeof(Fix) * FIX_CAP));
     if ((rc = grow(h, &st.recs, &st.recs_cap, rec_cap))) return rc;
     if ((rc = grow(h, &st.lost, &st.lost_cap, rec_cap))) return rc;
     if ((rc = grow(h, &st.tmp, &st.tmp_cap, rec_cap))) return rc;
@@ -181,18 +192,22 @@ int run_group(davis_handle *h, Stage &stage, Group &g, int gi, const uint8_t *de
     sp.conf_cap = stage.conf_cap;
     sp.hit_cap = g.hit_cap;
     sp.tbl_mask = (unsigned int)(stage.tbl_size - 1);
+    sp.mark_words = stage.mark_words;
+    sp.grp_cap = (unsigned int)std::min<size_t>(stage.glist_cap, 0xFFFFFFFFu);
 
     CU(cudaMemsetAsync(stage.ctr, 0, sizeof(Counters), st));
     CU(cudaMemsetAsync(stage.tbl, 0xFF, stage.tbl_size * sizeof(uint32_t), st));
     CU(cudaMemsetAsync(stage.lost, 0, g.hit_cap, st));
+    CU(cudaMemsetAsync(stage.marks, 0, sizeof(uint32_t) * (size_t)g.ns * stage.mark_words, st));
     CU(cudaEventRecord(g.ev[0], st));
     launch_demod(vw, stage.planes, g.ns, stage.tiles, stage.words_alloc, nullptr, 0, st);
     CU(cudaEventRecord(g.ev[1], st));
     launch_search(stage.planes, sp, stage.cand, stage.ctr, st);
     CU(cudaEventRecord(g.ev[2], st));
-    launch_precheck(vw, sp, stage.cand, stage.conf, stage.ctr, st);
-    launch_confirm(vw, sp, stage.planes, stage.conf, stage.recs, stage.tbl, stage.lost, stage.ctr,
-                   n_blocks, st);
+    launch_precheck(vw, sp, stage.cand, stage.conf, stage.marks, stage.glist, stage.ctr, st);
+    launch_exact(vw, sp, stage.planes, stage.glist, stage.fixes, stage.ctr, st);
+    launch_slice(vw, sp, stage.planes, stage.conf, stage.fixes, stage.recs, stage.tbl, stage.lost,
+                 stage.ctr, n_blocks, st);
     unsigned int *count = stage.per_stream, *start = count + g.ns, *fill = start + g.ns + 1;
     CU(cudaMemsetAsync(count, 0, sizeof(unsigned int) * g.ns, st));
     launch_finalize(vw, sp, stage.recs, stage.lost, stage.tmp, count, stage.ctr, st);
@@ -207,7 +222,7 @@ int run_group(davis_handle *h, Stage &stage, Group &g, int gi, const uint8_t *de
     CU(cudaEventRecord(g.ev[4], st));
     CU(cudaGetLastError());
     stage.last_group = gi;
-    h->stats.launches += 8 + (uint64_t)((g.ns + 65534) / 65535);
+    h->stats.launches += 9 + (uint64_t)((g.ns + 65534) / 65535);
     return DAVIS_OK;
 }
 
@@ -291,6 +306,9 @@ int davis_destroy(davis_handle *h) {
         if (s.planes) cudaFree(s.planes);
         if (s.cand) cudaFree(s.cand);
         if (s.conf) cudaFree(s.conf);
+        if (s.marks) cudaFree(s.marks);
+        if (s.glist) cudaFree(s.glist);
+        if (s.fixes) cudaFree(s.fixes);
         if (s.recs) cudaFree(s.recs);
         if (s.tbl) cudaFree(s.tbl);
         if (s.lost) cudaFree(s.lost);

@@ -131,6 +131,33 @@ __device__ __forceinline__ SpanSrc stage_span(const View &vw, int s, int v_begin
     return src;
 }
 
+// The same in two halves for spans of at most 32 chunks, so that the load of the next
+// span can be in flight while the current one is being used: span_chunk returns
+// this lane's 16 bytes, span_store puts them in shared memory.
+__device__ __forceinline__ uint4 span_chunk(const View &vw, int s, int v_begin, int n, int lane) {
+    const long long b0 = (2LL * v_begin) & ~15LL;
+    const long long b1 = 2LL * (v_begin + n);
+    const long long carry_bytes = 2LL * vw.n_carry, total = carry_bytes + 2LL * vw.n_new;
+    const long long off = b0 + 16LL * lane;
+    uint4 val = make_uint4(0u, 0u, 0u, 0u);
+    if (off < b1 && off >= 0 && off < total) {
+        const uint8_t *p = off < carry_bytes ? vw.carry + (size_t)s * vw.carry_stride + off
+                                             : vw.input + (size_t)s * vw.input_stride + (off - carry_bytes);
+        val = __ldg(reinterpret_cast<const uint4 *>(p));
+    }
+    return val;
+}
+__device__ __forceinline__ SpanSrc span_store(const View &vw, int s, int v_begin, uint4 val,
+                                              uint8_t *dst, int lane) {
+    reinterpret_cast<uint4 *>(dst)[lane] = val;
+    __syncwarp();
+    SpanSrc src;
+    src.base = dst;
+    src.v0 = (int)(((2LL * v_begin) & ~15LL) >> 1);
+    src.g0 = vw.blocks_done[s] * (int64_t)vw.block - vw.n_carry;
+    return src;
+}
+
 // rotated sample r[g] = lut(u) * j^(g mod 4); zero before the stream began
 template <class Src>
 __device__ __forceinline__ Cplx exact_rotated(const double *lut, const Src &src, int v) {
@@ -184,6 +211,62 @@ __device__ __forceinline__ void exact_filtered_run(const double *lut, const Src 
         }
         F[k] = f;
     }
+}
+
+// The same run with the rotation phase taken relative to the run's first sample
+// instead of the global sample index, and no test for the zero history: no
+// switch, no 64-bit index arithmetic.  Multiplying every sample by one power of j
+// maps each F[k] to j^p F[k], i.e. each component to +- a component (exactly:
+// rounding is symmetric), which leaves |F|^2 = re^2 + im^2 (addition commutes) and
+// the cross product im*re' - re*im' of two outputs of the run unchanged bit for
+// bit.  Valid only for quantities with that invariance and only when every
+// sample of the run exists (global index >= 0): see filtered_run below.
+template <int K>
+__device__ __forceinline__ Cplx fixed_rotated(double x, double y) {
+    if ((K & 3) == 0) return Cplx{x, y};
+    if ((K & 3) == 1) return Cplx{-y, x};
+    if ((K & 3) == 2) return Cplx{-x, -y};
+    return Cplx{y, -x};
+}
+template <int K, int N, class Src>
+struct FixedWindow {
+    static __device__ __forceinline__ void run(const double *lut, const Src &src, int v, Cplx (&r)[N]) {
+        const uchar2 u = src.at(v + K);
+        r[K] = fixed_rotated<K>(lut[u.x], lut[u.y]);
+        FixedWindow<K + 1, N, Src>::run(lut, src, v, r);
+    }
+};
+template <int N, class Src>
+struct FixedWindow<N, N, Src> {
+    static __device__ __forceinline__ void run(const double *, const Src &, int, Cplx (&)[N]) {}
+};
+
+template <int NF, class Src>
+__device__ __forceinline__ void fixed_filtered_run(const double *lut, const Src &src, int v_first,
+                                                   Cplx (&F)[NF]) {
+    const double taps[9] = {DAVIS_C0, DAVIS_C1, DAVIS_C2, DAVIS_C3, DAVIS_C4,
+                            DAVIS_C3, DAVIS_C2, DAVIS_C1, DAVIS_C0};
+    Cplx r[NF + 8];
+    FixedWindow<0, NF + 8, Src>::run(lut, src, v_first - 9, r);
+#pragma unroll
+    for (int k = 0; k < NF; k++) {
+        Cplx f{0.0, 0.0};
+#pragma unroll
+        for (int m = 0; m < 9; m++) {
+            f.re = __dadd_rn(f.re, __dmul_rn(taps[m], r[k + m].re));
+            f.im = __dadd_rn(f.im, __dmul_rn(taps[m], r[k + m].im));
+        }
+        F[k] = f;
+    }
+}
+
+// F[v_first + k], k < NF, for rotation-invariant uses: the fixed-phase run when all
+// its samples exist, the reference-phase run (zero history) otherwise.
+template <int NF, class Src>
+__device__ __forceinline__ void filtered_run(const double *lut, const Src &src, int v_first,
+                                             Cplx (&F)[NF]) {
+    if (v_first - 9 >= 0 && src.g0 + v_first - 9 >= 0) fixed_filtered_run<NF>(lut, src, v_first, F);
+    else exact_filtered_run<NF>(lut, src, v_first, F);
 }
 
 // numerator of D[g]: Im a * Re b - Re a * Im b,  a = F[g-1], b = F[g]

@@ -35,8 +35,10 @@ struct Counters {
     unsigned int n_conf;       // entries appended to the confirmed list
     unsigned int n_rec;        // records produced (before dedupe)
     unsigned int n_hit;        // packets written to the hit buffer (after dedupe)
-    unsigned int overflow;     // bit0 cand, bit1 conf, bit2 rec/hit
-    unsigned int pad[3];
+    unsigned int overflow;     // bit0 cand, bit1 conf, bit2 rec/hit, bit3 group list
+    unsigned int n_grp;        // bitmap word groups queued for the fp64 pass
+    unsigned int n_fix;        // bitmap words the fp64 pass changed
+    unsigned int pad;
 };
 
 struct SearchParams {
@@ -47,6 +49,18 @@ struct SearchParams {
     int n_streams;
     unsigned int cand_cap, conf_cap, hit_cap;
     unsigned int tbl_mask;     // dedupe hash table size - 1 (power of two)
+    int mark_words;            // 32-bit words of group marks per stream
+    unsigned int grp_cap;      // capacity of the group list
+};
+
+// The fp64 pass works on groups of GROUP_WORDS bitmap words (224 samples = 7 per lane).
+constexpr int GROUP_WORDS = 8;
+constexpr int GROUP_SAMPLES = GROUP_WORDS * LANE_SAMPLES;
+constexpr unsigned int FIX_CAP = 1024;
+
+// A bitmap word whose fp32 decisions differed from the reference's float64 ones.
+struct Fix {
+    uint32_t stream, word, diff, pad;
 };
 
 constexpr int DEMOD_WARPS = 8;
@@ -57,10 +71,12 @@ void launch_demod(const View &vw, uint32_t *words, int n_streams, int tiles, int
 void launch_search(const uint32_t *planes, const SearchParams &sp, Cand *cand, Counters *ctr,
                    cudaStream_t st);
 void launch_precheck(const View &vw, const SearchParams &sp, const Cand *cand, Cand *conf,
-                     Counters *ctr, cudaStream_t st);
-void launch_confirm(const View &vw, const SearchParams &sp, const uint32_t *planes,
-                    const Cand *conf, Rec *recs, uint32_t *tbl, uint8_t *lost, Counters *ctr,
-                    int n_blocks, cudaStream_t st);
+                     uint32_t *marks, uint2 *glist, Counters *ctr, cudaStream_t st);
+void launch_exact(const View &vw, const SearchParams &sp, uint32_t *planes, const uint2 *glist,
+                  Fix *fixes, Counters *ctr, cudaStream_t st);
+void launch_slice(const View &vw, const SearchParams &sp, const uint32_t *planes,
+                  const Cand *conf, const Fix *fixes, Rec *recs, uint32_t *tbl, uint8_t *lost,
+                  Counters *ctr, int n_blocks, cudaStream_t st);
 void launch_finalize(const View &vw, const SearchParams &sp, const Rec *recs, const uint8_t *lost,
                      davis_hit *hits, unsigned int *per_stream, Counters *ctr, cudaStream_t st);
 void launch_order(const davis_hit *tmp, const Counters *ctr, int stream0, int n_streams,

@@ -129,32 +129,153 @@ void launch_search(const uint32_t *words, const SearchParams &sp, Cand *cand, Co
 // k_precheck: one thread per candidate.  Exact fp32 matches pass; a candidate
 // with one disagreeing symbol passes only if the reference's float64 arithmetic
 // gives the sync word's bit there (i.e. the fp32 sign was the marginal one).
+// A passing candidate queues the bitmap word groups its 80 symbols live in
+// (samples v .. v + 14*79) for the fp64 pass; a group is queued once (mark bit).
 // ---------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
 k_precheck(View vw, SearchParams sp, const Cand *__restrict__ cand, Cand *__restrict__ conf,
-           Counters *ctr) {
+           uint32_t *__restrict__ marks, uint2 *__restrict__ glist, Counters *ctr) {
     __shared__ double lut[256];
     stage_lut(lut, vw.lut);
     const unsigned int n = min(ctr->n_cand, sp.cand_cap);
-    for (unsigned int i = blockIdx.x * blockDim.x + threadIdx.x; i < n;
-         i += gridDim.x * blockDim.x) {
-        Cand c = cand[i];
-        bool pass = c.miss < 0;
-        if (!pass) {
-            const uint32_t want = (sp.pat_rev >> c.miss) & 1u;
-            pass = exact_bit(lut, GlobalSrc(vw, (int)c.stream), c.v + SPS * c.miss) == want;
+    const int lane = threadIdx.x & 31;
+    const uint32_t below = (1u << lane) - 1u;
+    // warp-uniform trip count; list appends are aggregated to one atomic per warp
+    for (unsigned int i0 = blockIdx.x * blockDim.x + (threadIdx.x & ~31u); i0 < n;
+         i0 += gridDim.x * blockDim.x) {
+        const unsigned int i = i0 + lane;
+        Cand c{0u, 0, -1, 0u};
+        bool pass = false;
+        if (i < n) {
+            c = cand[i];
+            pass = c.miss < 0;
+            if (!pass) {
+                const uint32_t want = (sp.pat_rev >> c.miss) & 1u;
+                pass = exact_bit(lut, GlobalSrc(vw, (int)c.stream), c.v + SPS * c.miss) == want;
+            }
         }
+        const uint32_t pm = __ballot_sync(0xFFFFFFFFu, pass);
+        if (pm == 0) continue;
+        unsigned int at0 = 0;
+        if (lane == 0) at0 = atomicAdd(&ctr->n_conf, (unsigned int)__popc(pm));
+        at0 = __shfl_sync(0xFFFFFFFFu, at0, 0);
         if (pass) {
-            const unsigned int at = atomicAdd(&ctr->n_conf, 1u);
+            const unsigned int at = at0 + __popc(pm & below);
             if (at < sp.conf_cap) conf[at] = c;
-            else atomicOr(&ctr->overflow, 2u);
+            else { atomicOr(&ctr->overflow, 2u); pass = false; }
+        }
+        // groups this position needs that nobody queued yet
+        unsigned int fresh[8];
+        int n_fresh = 0;
+        if (pass) {
+            const int g0 = c.v / GROUP_SAMPLES, g1 = (c.v + SPS * (PKT_SYMS - 1)) / GROUP_SAMPLES;
+            uint32_t *row = marks + (size_t)c.stream * sp.mark_words;
+            for (int g = g0; g <= g1; g++) {
+                const uint32_t bit = 1u << (g & 31);
+                if (row[g >> 5] & bit) continue;                // cheap pre-test; atomicOr decides
+                if (atomicOr(&row[g >> 5], bit) & bit) continue;
+                fresh[n_fresh++] = (unsigned int)g;
+            }
+        }
+        unsigned int incl = (unsigned int)n_fresh;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const unsigned int y = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+            if (lane >= o) incl += y;
+        }
+        const unsigned int total = __shfl_sync(0xFFFFFFFFu, incl, 31);
+        if (total == 0) continue;
+        unsigned int ga0 = 0;
+        if (lane == 0) ga0 = atomicAdd(&ctr->n_grp, total);
+        ga0 = __shfl_sync(0xFFFFFFFFu, ga0, 0) + incl - (unsigned int)n_fresh;
+        for (int k = 0; k < n_fresh; k++) {
+            if (ga0 + k < sp.grp_cap) glist[ga0 + k] = make_uint2(c.stream, fresh[k]);
+            else atomicOr(&ctr->overflow, 8u);
         }
     }
 }
 
 void launch_precheck(const View &vw, const SearchParams &sp, const Cand *cand, Cand *conf,
-                     Counters *ctr, cudaStream_t st) {
-    k_precheck<<<148 * 4, 256, 0, st>>>(vw, sp, cand, conf, ctr);
+                     uint32_t *marks, uint2 *glist, Counters *ctr, cudaStream_t st) {
+    k_precheck<<<148 * 4, 256, 0, st>>>(vw, sp, cand, conf, marks, glist, ctr);
+}
+
+// ---------------------------------------------------------------------------
+// k_exact: one warp per queued group of GROUP_WORDS bitmap words (224 samples).
+// The group's decisions are recomputed in fp64 in the reference's operation order
+// and written over the fp32 ones, so everything downstream (sync check, slicing,
+// CRC) reads the reference's own bits.  Lane l decides the 7 samples
+// 224 g + 7 l .. + 6 from a register window of 16 samples (8 filter outputs).
+//
+// The rotation phase is taken relative to the lane's window: multiplying every
+// sample by the same power of j maps (F[n-1], F[n]) to (j^p F[n-1], j^p F[n]), each
+// component to +- a component (exactly: rounding is symmetric), and the cross
+// product im*re' - re*im' to the same two products in the same roles.  Only the
+// zero history of a fresh stream breaks that, and those groups take the generic
+// path (exact_bit).
+// ---------------------------------------------------------------------------
+constexpr int EXACT_WARPS = 8;
+constexpr int GRP_LANE = GROUP_SAMPLES / 32;                   // 7 decisions per lane
+
+__global__ void __launch_bounds__(EXACT_WARPS * 32)
+k_exact(View vw, SearchParams sp, uint32_t *__restrict__ planes, const uint2 *__restrict__ glist,
+        Fix *__restrict__ fixes, Counters *ctr) {
+    constexpr int SPAN = GROUP_SAMPLES + 10;
+    __shared__ double lut[256];
+    __shared__ uint4 span_mem[EXACT_WARPS][(2 * SPAN + 32 + 15) / 16];
+    stage_lut(lut, vw.lut);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const unsigned int n = min(ctr->n_grp, sp.grp_cap);
+    const unsigned int warps = gridDim.x * EXACT_WARPS;
+    // the next group's span is fetched into a register while this one is computed
+    unsigned int gi = blockIdx.x * EXACT_WARPS + warp;
+    uint2 e = gi < n ? glist[gi] : make_uint2(0u, 0u);
+    uint4 chunk = gi < n ? span_chunk(vw, (int)e.x, (int)e.y * GROUP_SAMPLES - 10, SPAN, lane)
+                         : make_uint4(0u, 0u, 0u, 0u);
+    for (; gi < n; gi += warps) {
+        const int s = (int)e.x, grp = (int)e.y;
+        const int v_begin = grp * GROUP_SAMPLES - 10;
+        __syncwarp();                                          // previous span fully consumed
+        const SpanSrc src = span_store(vw, s, v_begin, chunk,
+                                       reinterpret_cast<uint8_t *>(span_mem[warp]), lane);
+        if (gi + warps < n) {
+            e = glist[gi + warps];
+            chunk = span_chunk(vw, (int)e.x, (int)e.y * GROUP_SAMPLES - 10, SPAN, lane);
+        }
+        const int n0 = grp * GROUP_SAMPLES + GRP_LANE * lane;  // first sample this lane decides
+        uint32_t bits = 0;
+        if (v_begin < 0 || src.g0 + v_begin < 0) {             // zero history in reach: generic path
+#pragma unroll 1
+            for (int t = 0; t < GRP_LANE; t++) bits |= exact_bit(lut, src, n0 + t) << t;
+        } else {
+            Cplx F[GRP_LANE + 1];                              // F of V samples n0 - 1 .. n0 + 6
+            fixed_filtered_run<GRP_LANE + 1>(lut, src, n0 - 1, F);
+#pragma unroll
+            for (int t = 0; t < GRP_LANE; t++)
+                bits |= (uint32_t)((unsigned long long)__double_as_longlong(exact_cross(F[t], F[t + 1])) >> 63)
+                        << t;
+        }
+        // four lanes make one 28-bit word
+        uint32_t word = bits << (GRP_LANE * (lane & 3));
+        word |= __shfl_xor_sync(0xFFFFFFFFu, word, 1);
+        word |= __shfl_xor_sync(0xFFFFFFFFu, word, 2);
+        if ((lane & 3) == 0) {
+            const int wi = grp * GROUP_WORDS + (lane >> 2);
+            uint32_t *p = planes + (size_t)s * sp.words_alloc + wi;
+            const uint32_t diff = (*p ^ word) & MASK28;
+            *p = word;
+            // words past the end of the call's samples hold no decisions anyone reads
+            if (diff && (long long)LANE_SAMPLES * (wi + 1) <= (long long)vw.n_carry + vw.n_new) {
+                const unsigned int at = atomicAdd(&ctr->n_fix, 1u);
+                if (at < FIX_CAP) fixes[at] = Fix{(uint32_t)s, (uint32_t)wi, diff, 0u};
+            }
+        }
+    }
+}
+
+void launch_exact(const View &vw, const SearchParams &sp, uint32_t *planes, const uint2 *glist,
+                  Fix *fixes, Counters *ctr, cudaStream_t st) {
+    k_exact<<<148 * 4, EXACT_WARPS * 32, 0, st>>>(vw, sp, planes, glist, fixes, ctr);
 }
 
 // ---------------------------------------------------------------------------
@@ -218,12 +339,14 @@ __device__ void dedupe_insert(const Rec *recs, uint32_t id, uint32_t *tbl, uint3
 }
 
 // ---------------------------------------------------------------------------
-// k_confirm: one warp per surviving candidate.  All 80 symbols are decided in
-// fp64 in the reference's operation order; the first 16 must equal the sync
-// word.  Then: pack MSB-first (dsp.py:197-200), bit-reverse each byte and run
-// the table CRC over bytes 2..9 (protocol.py:290-297, crc.py:19-26), and emit
-// one record per reference call whose window holds the position at index <=
-// block_size (dsp.py:194), entering each into the dedupe table.
+// k_slice: one thread per surviving candidate, after k_exact has replaced the
+// decisions it needs by the reference's float64 ones.  The 80 symbols are read
+// from the bitmap (symbol i of position 28w + b: bit b of word w + i/2 for even i,
+// of the half-step word for odd i); the first 16 must equal the sync word.  Then:
+// pack MSB-first (dsp.py:197-200), bit-reverse each byte and run the table CRC
+// over bytes 2..9 (protocol.py:290-297, crc.py:19-26), and emit one record per
+// reference call whose window holds the position at index <= block_size
+// (dsp.py:194), entering each into the dedupe table.
 // ---------------------------------------------------------------------------
 __device__ __forceinline__ double warp_sum(double x) {
 #pragma unroll
@@ -231,60 +354,65 @@ __device__ __forceinline__ double warp_sum(double x) {
     return x;
 }
 
-constexpr int CONFIRM_WARPS = 8;
-
-__global__ void __launch_bounds__(CONFIRM_WARPS * 32)
-k_confirm(View vw, SearchParams sp, const uint32_t *__restrict__ planes,
-          const Cand *__restrict__ conf, Rec *recs, uint32_t *tbl, uint8_t *lost, Counters *ctr,
-          int n_blocks) {
-    constexpr int SPAN = SPS * PKT_SYMS + 16;                  // 80 symbols + FIR history
+__global__ void __launch_bounds__(256)
+k_slice(View vw, SearchParams sp, const uint32_t *__restrict__ planes,
+        const Cand *__restrict__ conf, const Fix *__restrict__ fixes, Rec *recs, uint32_t *tbl,
+        uint8_t *lost, Counters *ctr, int n_blocks) {
     __shared__ uint16_t tbl16[256];
-    __shared__ double lut[256];
-    __shared__ uint4 span_mem[CONFIRM_WARPS][(2 * SPAN + 32 + 15) / 16];
     for (int i = threadIdx.x; i < 256; i += blockDim.x) {      // crc.py:28-42, poly 0x1021
         uint32_t reg = (uint32_t)i << 8;
 #pragma unroll
         for (int b = 0; b < 8; b++) reg = (reg & 0x8000u) ? ((reg << 1) ^ 0x1021u) : (reg << 1);
         tbl16[i] = (uint16_t)reg;
     }
-    stage_lut(lut, vw.lut);
-
-    const int lane = threadIdx.x & 31;
+    __syncthreads();
     const unsigned int n = min(ctr->n_conf, sp.conf_cap);
-    const unsigned int warps = gridDim.x * CONFIRM_WARPS;
-    for (unsigned int ci = blockIdx.x * CONFIRM_WARPS + (threadIdx.x >> 5); ci < n; ci += warps) {
+    const unsigned int n_fix = min(ctr->n_fix, FIX_CAP);
+    const bool fix_lost = ctr->n_fix > FIX_CAP;
+    for (unsigned int ci = blockIdx.x * blockDim.x + threadIdx.x; ci < n;
+         ci += gridDim.x * blockDim.x) {
         const Cand c = conf[ci];
         const int s = (int)c.stream;
-        __syncwarp();                                          // previous span fully consumed
-        const SpanSrc src = stage_span(vw, s, c.v - 10, SPAN,
-                                       reinterpret_cast<uint8_t *>(span_mem[threadIdx.x >> 5]), lane);
-        uint32_t m[3];
-        uint32_t disagree = 0;
-#pragma unroll
-        for (int part = 0; part < 3; part++) {
-            const int i = lane + 32 * part;
-            uint32_t bit = 0, fast = 0;
-            if (i < PKT_SYMS) {
-                const int v = c.v + SPS * i;
-                bit = exact_bit(lut, src, v);
-                const int wd = v / LANE_SAMPLES;
-                fast = (planes[(size_t)s * sp.words_alloc + wd] >> (v - wd * LANE_SAMPLES)) & 1u;
-            }
-            m[part] = __ballot_sync(0xFFFFFFFFu, bit);
-            disagree |= __ballot_sync(0xFFFFFFFFu, bit != fast);
+        const int w = c.v / LANE_SAMPLES, b = c.v - w * LANE_SAMPLES;
+        const uint32_t *row = planes + (size_t)s * sp.words_alloc + w;
+        // symbols 0..79 in arrival order, symbol i in bit i
+        unsigned long long lo = 0;
+        uint32_t hi = 0;
+        uint32_t e0 = row[0];
+#pragma unroll 8
+        for (int m = 0; m < PKT_SYMS / 2; m++) {
+            const uint32_t e1 = row[m + 1];
+            const uint32_t h = (e0 >> SPS) | (e1 << SPS);
+            const unsigned long long two = ((e0 >> b) & 1u) | (((h >> b) & 1u) << 1);
+            if (m < 32) lo |= two << (2 * m);
+            else hi |= (uint32_t)two << (2 * (m - 32));
+            e0 = e1;
         }
-        if ((m[0] & 0xFFFFu) != sp.pat_rev) continue;          // not a match in float64
-        if (lane != 0) continue;
+        if (((uint32_t)lo & 0xFFFFu) != sp.pat_rev) continue;  // not a match in float64
 
-        // host-order byte b is the 8 symbols in arrival order, LSB first; the
+        // did the fp64 pass change one of this packet's decisions?
+        uint32_t corrected = fix_lost ? 2u : 0u;
+        for (unsigned int f = 0; f < n_fix; f++) {
+            const Fix fx = fixes[f];
+            const int m = (int)fx.word - w;
+            if (fx.stream != (uint32_t)s || m < 0 || m > PKT_SYMS / 2) continue;
+            uint32_t used = 0;
+            if (m < PKT_SYMS / 2) used |= (1u << b) | (b < SPS ? 1u << (b + SPS) : 0u);
+            if (m >= 1 && b >= SPS) used |= 1u << (b - SPS);
+            if (fx.diff & used) corrected |= 1u;
+        }
+
+        // host-order byte k is the 8 symbols in arrival order, LSB first; the
         // on-air (Packet.data) byte is its bit reversal.
         uint8_t host[PKT_BYTES];
 #pragma unroll
-        for (int b = 0; b < PKT_BYTES; b++) host[b] = (uint8_t)(m[b >> 2] >> (8 * (b & 3)));
+        for (int k = 0; k < 8; k++) host[k] = (uint8_t)(lo >> (8 * k));
+        host[8] = (uint8_t)hi;
+        host[9] = (uint8_t)(hi >> 8);
         uint32_t reg = 0;
 #pragma unroll
-        for (int b = 2; b < PKT_BYTES; b++)
-            reg = ((reg << 8) & 0xFFFFu) ^ tbl16[(reg >> 8) ^ host[b]];
+        for (int k = 2; k < PKT_BYTES; k++)
+            reg = ((reg << 8) & 0xFFFFu) ^ tbl16[(reg >> 8) ^ host[k]];
 
         const int64_t B = vw.block, W = vw.window_blocks;
         const int64_t done = vw.blocks_done[s];
@@ -302,9 +430,9 @@ k_confirm(View vw, SearchParams sp, const uint32_t *__restrict__ planes,
             r.call = (uint32_t)k;
             r.index = (int32_t)idx;
 #pragma unroll
-            for (int b = 0; b < PKT_BYTES; b++) r.data[b] = (uint8_t)(__brev((uint32_t)host[b]) >> 24);
+            for (int q = 0; q < PKT_BYTES; q++) r.data[q] = (uint8_t)(__brev((uint32_t)host[q]) >> 24);
             r.crc_ok = reg == 0;
-            r.flags = disagree ? 1 : 0;
+            r.flags = (uint8_t)corrected;
             r.pad[0] = r.pad[1] = r.pad[2] = 0;
             recs[at] = r;
             __threadfence();                                   // publish before the id is visible
@@ -313,11 +441,10 @@ k_confirm(View vw, SearchParams sp, const uint32_t *__restrict__ planes,
     }
 }
 
-void launch_confirm(const View &vw, const SearchParams &sp, const uint32_t *planes,
-                    const Cand *conf, Rec *recs, uint32_t *tbl, uint8_t *lost, Counters *ctr,
-                    int n_blocks, cudaStream_t st) {
-    k_confirm<<<148 * 4, CONFIRM_WARPS * 32, 0, st>>>(vw, sp, planes, conf, recs, tbl, lost, ctr,
-                                                      n_blocks);
+void launch_slice(const View &vw, const SearchParams &sp, const uint32_t *planes,
+                  const Cand *conf, const Fix *fixes, Rec *recs, uint32_t *tbl, uint8_t *lost,
+                  Counters *ctr, int n_blocks, cudaStream_t st) {
+    k_slice<<<148 * 4, 256, 0, st>>>(vw, sp, planes, conf, fixes, recs, tbl, lost, ctr, n_blocks);
 }
 
 // ---------------------------------------------------------------------------
@@ -326,6 +453,8 @@ void launch_confirm(const View &vw, const SearchParams &sp, const uint32_t *plan
 // one-block `filtered` buffer indexed by two-block window positions) and the
 // discriminator mean Parser.parse takes (protocol.py:304-310), all in fp64.
 // ---------------------------------------------------------------------------
+constexpr int CONFIRM_WARPS = 8;
+
 // sum of |F|^2 over V indices [v0, v1), v1 - v0 <= 32 * FIN_CHUNK; lane l takes the
 // FIN_CHUNK consecutive positions starting at v0 + FIN_CHUNK * l
 constexpr int FIN_CHUNK = 7;                                   // 224 / 32
@@ -335,7 +464,7 @@ __device__ double power_sum(const double *lut, const SpanSrc &src, int v0, int v
     const int a = v0 + FIN_CHUNK * lane;
     if (a < v1) {
         Cplx F[FIN_CHUNK];
-        exact_filtered_run<FIN_CHUNK>(lut, src, a, F);
+        filtered_run<FIN_CHUNK>(lut, src, a, F);
 #pragma unroll
         for (int k = 0; k < FIN_CHUNK; k++)
             if (a + k < v1) acc += F[k].re * F[k].re + F[k].im * F[k].im;
@@ -347,7 +476,7 @@ __device__ double power_sum(const double *lut, const SpanSrc &src, int v0, int v
 __device__ double disc_sum(const double *lut, const SpanSrc &src, int v0, int lane) {
     const int a = v0 + FIN_CHUNK * lane;
     Cplx F[FIN_CHUNK + 1];
-    exact_filtered_run<FIN_CHUNK + 1>(lut, src, a - 1, F);
+    filtered_run<FIN_CHUNK + 1>(lut, src, a - 1, F);
     double acc = 0.0;
 #pragma unroll
     for (int k = 0; k < FIN_CHUNK; k++)
