@@ -250,11 +250,14 @@ __device__ __forceinline__ void fixed_filtered_run(const double *lut, const Src 
     FixedWindow<0, NF + 8, Src>::run(lut, src, v_first - 9, r);
 #pragma unroll
     for (int k = 0; k < NF; k++) {
-        Cplx f{0.0, 0.0};
+        // m = 0..8 in order, each step one fused multiply-add: np.convolve hands the sum to
+        // a BLAS dot product whose rounding order is unspecified, so the reference defines
+        // F only to a few ulp; the fused form is inside that and halves the fp64 work.
+        Cplx f{__dmul_rn(taps[0], r[k].re), __dmul_rn(taps[0], r[k].im)};
 #pragma unroll
-        for (int m = 0; m < 9; m++) {
-            f.re = __dadd_rn(f.re, __dmul_rn(taps[m], r[k + m].re));
-            f.im = __dadd_rn(f.im, __dmul_rn(taps[m], r[k + m].im));
+        for (int m = 1; m < 9; m++) {
+            f.re = __fma_rn(taps[m], r[k + m].re, f.re);
+            f.im = __fma_rn(taps[m], r[k + m].im, f.im);
         }
         F[k] = f;
     }

@@ -5,6 +5,8 @@
 // dsp/dsp.go:105-131 + dsp/search.go:104-119), Demodulator._slice
 // (dsp.py:190-246; Go dsp/dsp.go:138-169) and the CRC gate of Parser.parse
 // (src/rtldavis/protocol.py:290-300 with crc.py:19-42 and protocol.py:79-83).
+#include <algorithm>
+
 #include "davis_kernels.cuh"
 
 namespace davis {
@@ -24,105 +26,179 @@ namespace davis {
 // be lost.  k_precheck settles such positions in fp64.
 // ---------------------------------------------------------------------------
 constexpr int SEARCH_THREADS = 256;
-constexpr int STAGE = 128;   // per-block staging slots for found candidates
 constexpr uint32_t MASK28 = 0x0FFFFFFFu;
 
-template <typename T>
-__device__ __forceinline__ void block_flush(T *stage, int n_staged, T *out, unsigned int *counter,
-                                            unsigned int cap, unsigned int *overflow,
-                                            unsigned int flag, unsigned int *s_base) {
-    __syncthreads();
-    if (n_staged == 0) return;
-    if (threadIdx.x == 0) *s_base = atomicAdd(counter, (unsigned int)n_staged);
-    __syncthreads();
-    const unsigned int base = *s_base;
-    for (int i = threadIdx.x; i < n_staged; i += blockDim.x) {
-        if (base + i < cap) out[base + i] = stage[i];
-        else atomicOr(overflow, flag);
+constexpr int SEARCH_WORDS = 4;      // bitmap words per thread (one 16-byte load + 8 words of lookahead)
+constexpr int SEARCH_WARPS = SEARCH_THREADS / 32;
+constexpr int QUEUE = 160;           // per-warp queue of positions that passed the prefilter
+
+// Second stage, dense: every lane takes one queued position (stream, word, bit), reads the
+// nine bitmap words its 16 symbols live in, counts the differing symbols exactly and stages
+// the position as a candidate if at most one differs.
+__device__ __forceinline__ bool search_check(const uint32_t *__restrict__ words, const SearchParams &sp,
+                                             unsigned long long entry, Cand &c) {
+    const int s = (int)(entry >> 32);
+    const int w = (int)((uint32_t)entry >> 5), b = (int)(entry & 31u);
+    const int v = LANE_SAMPLES * w + b;
+    if (v < sp.v_lo || v > sp.v_hi) return false;
+    const uint32_t *row = words + (size_t)s * sp.words_alloc + w;
+    uint32_t win = 0;
+    uint32_t e0 = __ldg(row);
+#pragma unroll
+    for (int m = 0; m < PRE_SYMS / 2; m++) {
+        const uint32_t e1 = __ldg(row + m + 1);
+        const uint32_t h = (e0 >> SPS) | (e1 << SPS);
+        win |= (((e0 >> b) & 1u) | (((h >> b) & 1u) << 1)) << (2 * m);
+        e0 = e1;
+    }
+    const uint32_t diff = win ^ sp.pat_rev;
+    if (diff & (diff - 1)) return false;                      // two or more symbols differ
+    c.stream = (uint32_t)s;
+    c.v = v;
+    c.miss = diff ? __ffs(diff) - 1 : -1;
+    c.pad = 0;
+    return true;
+}
+
+// the warp checks its queued positions and appends the candidates with one atomic per round
+__device__ __forceinline__ void search_drain(const uint32_t *__restrict__ words, const SearchParams &sp,
+                                             const unsigned long long *q, int qn, int lane,
+                                             Cand *__restrict__ cand, Counters *ctr) {
+    const uint32_t below = (1u << lane) - 1u;
+    for (int i0 = 0; i0 < qn; i0 += 32) {
+        Cand c;
+        const bool ok = i0 + lane < qn && search_check(words, sp, q[i0 + lane], c);
+        const uint32_t m = __ballot_sync(0xFFFFFFFFu, ok);
+        if (m == 0) continue;
+        unsigned int at = 0;
+        if (lane == 0) at = atomicAdd(&ctr->n_cand, (unsigned int)__popc(m));
+        at = __shfl_sync(0xFFFFFFFFu, at, 0) + __popc(m & below);
+        if (ok) {
+            if (at < sp.cand_cap) cand[at] = c;
+            else atomicOr(&ctr->overflow, 1u);
+        }
     }
 }
 
-constexpr int SEARCH_WORDS = 4;      // bitmap words per thread (one 16-byte load + 8 words of lookahead)
-
 __global__ void __launch_bounds__(SEARCH_THREADS)
-k_search(const uint32_t *__restrict__ words, SearchParams sp, Cand *__restrict__ cand,
-         Counters *ctr) {
-    __shared__ Cand stage[STAGE];
-    __shared__ int n_stage;
-    __shared__ unsigned int s_base;
-    if (threadIdx.x == 0) n_stage = 0;
-    __syncthreads();
-
+k_search(const uint32_t *__restrict__ words, SearchParams sp, unsigned int s_off,
+         Cand *__restrict__ cand, Counters *ctr) {
+    __shared__ unsigned long long queue[SEARCH_WARPS][QUEUE];
+    const int lane = threadIdx.x & 31;
+    unsigned long long *q = queue[threadIdx.x >> 5];
     const int quads = (sp.words + SEARCH_WORDS - 1) / SEARCH_WORDS;
-    const long long id = (long long)blockIdx.x * SEARCH_THREADS + threadIdx.x;
-    const int s = (int)(id / quads);
-    const int w0 = (int)(id - (long long)s * quads) * SEARCH_WORDS;
+    const long long total = (long long)sp.n_streams * quads;
+    // literal masks of the sync word: symbol i must be 1 -> 0, must be 0 -> ~0
+    uint32_t inv[PRE_SYMS];
+#pragma unroll
+    for (int i = 0; i < PRE_SYMS; i++) inv[i] = ((sp.pat_rev >> i) & 1u) ? 0u : 0xFFFFFFFFu;
 
-    if (s < sp.n_streams) {
-        // literal masks of the sync word: symbol i must be 1 -> 0, must be 0 -> ~0
-        uint32_t inv[PRE_SYMS];
-#pragma unroll
-        for (int i = 0; i < PRE_SYMS; i++) inv[i] = ((sp.pat_rev >> i) & 1u) ? 0u : 0xFFFFFFFFu;
+    int qn = 0;
+    // warp-uniform trip count: id0 is the warp's first thread
+    for (long long id0 = (long long)blockIdx.x * SEARCH_THREADS + (threadIdx.x & ~31);
+         id0 < total; id0 += (long long)gridDim.x * SEARCH_THREADS) {
+        const long long id = id0 + lane;
+        const unsigned int sl = (unsigned int)id / (unsigned int)quads;          // total < 2^31 (launch_search)
+        const int w0 = (int)((unsigned int)id - sl * (unsigned int)quads) * SEARCH_WORDS;
+        const unsigned int s = s_off + sl;
 
-        const uint4 *base = reinterpret_cast<const uint4 *>(words + (size_t)s * sp.words_alloc + w0);
-        uint32_t e[SEARCH_WORDS + 8], h[SEARCH_WORDS + 7];
+        // First stage, word-parallel.  At most one differing symbol means the first
+        // eight or the last eight symbols match exactly: two AND chains (one LOP3 per
+        // symbol) find those positions for all 28 phases of a word at once (2 * 2^-8
+        // of the positions of noise).
+        uint32_t hit[SEARCH_WORDS];
 #pragma unroll
-        for (int k = 0; k < (SEARCH_WORDS + 8) / 4; k++) {
-            const uint4 t = __ldg(base + k);
-            e[4 * k] = t.x; e[4 * k + 1] = t.y; e[4 * k + 2] = t.z; e[4 * k + 3] = t.w;
-        }
+        for (int k = 0; k < SEARCH_WORDS; k++) hit[k] = 0;
+        if (id < total) {
+            const uint4 *base = reinterpret_cast<const uint4 *>(words + (size_t)s * sp.words_alloc + w0);
+            uint32_t e[SEARCH_WORDS + 8], h[SEARCH_WORDS + 7];
 #pragma unroll
-        for (int m = 0; m < SEARCH_WORDS + 7; m++) h[m] = (e[m] >> SPS) | (e[m + 1] << SPS);
-#pragma unroll
-        for (int k = 0; k < SEARCH_WORDS; k++) {
-            // word-parallel mismatch counter saturating at two: c1 = "some symbol
-            // differs", c2 = "two or more differ", for all 28 positions at once
-            uint32_t c1 = 0, c2 = 0;
-#pragma unroll
-            for (int m = 0; m < 8; m++) {
-                const uint32_t de = ~(e[k + m] ^ inv[2 * m]);
-                c2 |= c1 & de;
-                c1 |= de;
-                const uint32_t dh = ~(h[k + m] ^ inv[2 * m + 1]);
-                c2 |= c1 & dh;
-                c1 |= dh;
+            for (int k = 0; k < (SEARCH_WORDS + 8) / 4; k++) {
+                const uint4 t = __ldg(base + k);
+                e[4 * k] = t.x; e[4 * k + 1] = t.y; e[4 * k + 2] = t.z; e[4 * k + 3] = t.w;
             }
-            uint32_t hit = ~c2 & MASK28;
-            while (hit) {
-                const int b = __ffs(hit) - 1;
-                hit &= hit - 1;
-                const int v = LANE_SAMPLES * (w0 + k) + b;
-                if (v < sp.v_lo || v > sp.v_hi) continue;
-                uint32_t win = 0;
 #pragma unroll
-                for (int i = 0; i < PRE_SYMS; i++)
-                    win |= ((((i & 1) ? h[k + (i >> 1)] : e[k + (i >> 1)]) >> b) & 1u) << i;
-                const uint32_t diff = win ^ sp.pat_rev;           // at most one bit set
-                Cand c;
-                c.stream = (uint32_t)s;
-                c.v = v;
-                c.miss = diff ? __ffs(diff) - 1 : -1;
-                c.pad = 0;
-                const int slot = atomicAdd(&n_stage, 1);
-                if (slot < STAGE) stage[slot] = c;
-                else {                                    // staging full: append directly
-                    const unsigned int at = atomicAdd(&ctr->n_cand, 1u);
-                    if (at < sp.cand_cap) cand[at] = c;
-                    else atomicOr(&ctr->overflow, 1u);
+            for (int m = 0; m < SEARCH_WORDS + 7; m++) h[m] = (e[m] >> SPS) | (e[m + 1] << SPS);
+#pragma unroll
+            for (int k = 0; k < SEARCH_WORDS; k++) {
+                uint32_t first = MASK28, last = MASK28;
+#pragma unroll
+                for (int m = 0; m < 4; m++) {
+                    first &= e[k + m] ^ inv[2 * m];
+                    first &= h[k + m] ^ inv[2 * m + 1];
+                    last &= e[k + 4 + m] ^ inv[8 + 2 * m];
+                    last &= h[k + 4 + m] ^ inv[8 + 2 * m + 1];
+                }
+                hit[k] = first | last;
+            }
+        }
+
+        // Compact the surviving positions of the whole warp into its queue (one
+        // exclusive scan of the per-lane counts, then every lane writes its own);
+        // the queue is checked densely (every lane one position) when it fills up.
+        const int mine = __popc(hit[0]) + __popc(hit[1]) + __popc(hit[2]) + __popc(hit[3]);
+        int incl = mine;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int y = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+            if (lane >= o) incl += y;
+        }
+        const int all = __shfl_sync(0xFFFFFFFFu, incl, 31);
+        if (all == 0) continue;
+        if (qn + all > QUEUE) {                               // make room first
+            __syncwarp();
+            search_drain(words, sp, q, qn, lane, cand, ctr);
+            __syncwarp();
+            qn = 0;
+        }
+        if (all > QUEUE) {                                    // pathological input: no queueing
+#pragma unroll
+            for (int k = 0; k < SEARCH_WORDS; k++) {
+                for (;;) {
+                    const bool has = hit[k] != 0;
+                    if (__ballot_sync(0xFFFFFFFFu, has) == 0) break;
+                    unsigned long long e1 = 0;
+                    if (has) {
+                        e1 = ((unsigned long long)s << 32) | ((uint32_t)(w0 + k) << 5) | (uint32_t)(__ffs(hit[k]) - 1);
+                        hit[k] &= hit[k] - 1;
+                    }
+                    q[lane] = has ? e1 : 0ull;
+                    __syncwarp();
+                    // absent lanes queue position 0, which fails the range test (v_lo = HALO)
+                    search_drain(words, sp, q, 32, lane, cand, ctr);
+                    __syncwarp();
                 }
             }
+            continue;
         }
+        int at = qn + incl - mine;
+#pragma unroll
+        for (int k = 0; k < SEARCH_WORDS; k++) {
+            uint32_t hk = hit[k];
+            while (hk) {
+                q[at++] = ((unsigned long long)s << 32) | ((uint32_t)(w0 + k) << 5) | (uint32_t)(__ffs(hk) - 1);
+                hk &= hk - 1;
+            }
+        }
+        qn += all;
     }
-    __syncthreads();
-    block_flush(stage, min(n_stage, STAGE), cand, &ctr->n_cand, sp.cand_cap, &ctr->overflow, 1u,
-                &s_base);
+    __syncwarp();
+    search_drain(words, sp, q, qn, lane, cand, ctr);
 }
 
 void launch_search(const uint32_t *words, const SearchParams &sp, Cand *cand, Counters *ctr,
                    cudaStream_t st) {
-    const long long total = (long long)sp.n_streams * ((sp.words + SEARCH_WORDS - 1) / SEARCH_WORDS);
-    const unsigned grid = (unsigned)((total + SEARCH_THREADS - 1) / SEARCH_THREADS);
-    if (grid) k_search<<<grid, SEARCH_THREADS, 0, st>>>(words, sp, cand, ctr);
+    const long long quads = (sp.words + SEARCH_WORDS - 1) / SEARCH_WORDS;
+    if (quads == 0) return;
+    // 32-bit unit indices inside the kernel: at most 2^31 units per launch
+    const long long per_launch = std::max<long long>(1, (1LL << 31) / quads);
+    for (long long s0 = 0; s0 < sp.n_streams; s0 += per_launch) {
+        SearchParams part = sp;
+        part.n_streams = (int)std::min<long long>(per_launch, sp.n_streams - s0);
+        const long long total = part.n_streams * quads;
+        const unsigned grid = (unsigned)std::min<long long>((total + SEARCH_THREADS - 1) / SEARCH_THREADS, 148LL * 8);
+        k_search<<<grid, SEARCH_THREADS, 0, st>>>(words, part, (unsigned int)s0, cand, ctr);
+    }
 }
 
 // ---------------------------------------------------------------------------
