@@ -151,3 +151,40 @@ def make_batch(n_streams: int, n_samples: int, n_packets: int, snr_db: float = 3
         out[s] = cap.iq
         truth.append(cap.packets)
     return out, truth
+
+
+def make_hop_set(n_channels: int, n_samples: int, n_transmitters: int, hop_samples: int,
+                 snr_db: float = 30.0, seed: int = 0, df_range_hz: float = 3000.0
+                 ) -> Tuple[np.ndarray, List[List[Embedded]]]:
+    """BASELINE config 3: ``n_channels`` parallel narrowband streams (one per channel
+    of the hop set, src/rtldavis/protocol.py:119-171).  Transmitter t sends one packet
+    every ``hop_samples`` samples and moves to the next channel of its hop pattern
+    (a seeded permutation standing in for protocol.py:173-225, which is itself a
+    permutation of the channel indices) after each one, so every packet appears on
+    exactly one stream.  Each channel has a fixed residual carrier offset."""
+    rng = np.random.default_rng(seed)
+    df = rng.uniform(-df_range_hz, df_range_hz, size=n_channels)
+    pattern = rng.permutation(n_channels)
+    x = np.zeros((n_channels, n_samples), dtype=np.complex128)
+    truth: List[List[Embedded]] = [[] for _ in range(n_channels)]
+    burst_len = BURST_BITS * SPS + 2
+    for t in range(n_transmitters):
+        offset = int(rng.integers(0, hop_samples))
+        hop0 = int(rng.integers(0, n_channels))
+        k = 0
+        while True:
+            s = offset + k * hop_samples + int(rng.integers(0, SPS))
+            if s + burst_len >= n_samples:
+                break
+            ch = int(pattern[(hop0 + k) % n_channels])
+            msg = make_message(t % 8, int(rng.integers(2, 11)), rng.integers(0, 256, size=5))
+            w = burst_waveform(msg, float(df[ch]), 0.0, phase0=float(rng.uniform(0, 2 * np.pi)))
+            x[ch, s:s + w.size] += AMPLITUDE * w
+            truth[ch].append(Embedded(s, msg))
+            k += 1
+    sigma = AMPLITUDE / np.sqrt(2.0) * 10 ** (-snr_db / 20.0)
+    out = np.empty((n_channels, 2 * n_samples), dtype=np.uint8)
+    for ch in range(n_channels):
+        noise = sigma * (rng.standard_normal(n_samples) + 1j * rng.standard_normal(n_samples))
+        out[ch] = to_u8(x[ch] + noise)
+    return out, truth
