@@ -123,10 +123,18 @@ DAVIS_API int davis_reset(davis_handle *h, int stream);
 DAVIS_API int davis_demod_u8(davis_handle *h, const uint8_t *iq, size_t bytes_per_stream,
                    size_t stream_stride, int n_blocks, void *cuda_stream);
 
-/* Same for complex64 input (interleaved float re, im), the live pyrtlsdr entry,
- * src/rtldavis/dsp.py:144-150.  samples_per_stream = n_blocks * block_size. */
+/* Same for complex input, the live pyrtlsdr entry, src/rtldavis/dsp.py:144-151
+ * (`dest[:] = input_data`: the samples are used as they are, no LUT).  complex64 is
+ * interleaved float re, im; complex128 interleaved double re, im (what pyrtlsdr's
+ * read_samples returns and what worker.py:49 passes on).  samples_per_stream =
+ * n_blocks * block_size.  Every decision of this entry is made in float64 in the
+ * reference's operation order (there is no fp32 streaming form for arbitrary complex
+ * samples).  The carried tail is kept in the input's element type, so the input type
+ * may change only on a fresh or reset handle (DAVIS_E_STATE otherwise). */
 DAVIS_API int davis_demod_c64(davis_handle *h, const float *iq, size_t samples_per_stream,
                     size_t stream_stride_bytes, int n_blocks, void *cuda_stream);
+DAVIS_API int davis_demod_c128(davis_handle *h, const double *iq, size_t samples_per_stream,
+                     size_t stream_stride_bytes, int n_blocks, void *cuda_stream);
 
 /* Waits for the queued call and returns its packets: the concatenation, stream by
  * stream and call by call, of what the reference returns (search order of

@@ -38,7 +38,7 @@ HIT_DTYPE = np.dtype([("position", "<i8"), ("stream", "<u4"), ("call", "<u4"), (
 assert HIT_DTYPE.itemsize == 56
 
 EXPORTS = ["davis_abi_version", "davis_create", "davis_destroy", "davis_reset", "davis_demod_u8",
-           "davis_demod_c64", "davis_fetch_hits", "davis_fetch_hits_view", "davis_get_stats", "davis_debug_bits",
+           "davis_demod_c64", "davis_demod_c128", "davis_fetch_hits", "davis_fetch_hits_view", "davis_get_stats", "davis_debug_bits",
            "davis_debug_disc", "davis_debug_disc32", "davis_host_alloc", "davis_host_free",
            "davis_crc16_batch", "davis_last_error", "davis_strerror",
            "davis_synth_fill", "davis_synth_truth"]
@@ -76,6 +76,7 @@ def load() -> C.CDLL:
     L.davis_reset.argtypes = [vp, i32]
     L.davis_demod_u8.argtypes = [vp, vp, sz, sz, i32, vp]
     L.davis_demod_c64.argtypes = [vp, vp, sz, sz, i32, vp]
+    L.davis_demod_c128.argtypes = [vp, vp, sz, sz, i32, vp]
     L.davis_fetch_hits.argtypes = [vp, vp, sz, C.POINTER(sz)]
     L.davis_fetch_hits_view.argtypes = [vp, C.POINTER(vp), C.POINTER(sz)]
     L.davis_get_stats.argtypes = [vp, C.POINTER(DavisStats)]

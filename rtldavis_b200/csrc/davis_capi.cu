@@ -53,6 +53,7 @@ struct davis_handle {
     int n_streams = 0, device = 0;
     int B = 0, W = 0, n_carry = 0, n_keep = 0;       // samples
     size_t carry_stride = 0;
+    int elem = 2;                                     // bytes per sample of the current input type
     uint8_t *carry[2] = {nullptr, nullptr};
     int cur = 0;
     int64_t *d_blocks_done = nullptr;
@@ -169,7 +170,7 @@ void release_groups(davis_handle *h) {
 int run_group(davis_handle *h, Stage &stage, Group &g, int gi, const uint8_t *dev_input,
               size_t input_stride, int n_blocks, cudaStream_t st) {
     View vw;
-    vw.carry = h->carry[h->cur] + (size_t)g.s0 * h->carry_stride + 2 * (size_t)(h->n_keep - h->n_carry);
+    vw.carry = h->carry[h->cur] + (size_t)g.s0 * h->carry_stride + h->elem * (size_t)(h->n_keep - h->n_carry);
     vw.input = dev_input;
     vw.carry_stride = h->carry_stride;
     vw.input_stride = input_stride;
@@ -180,6 +181,8 @@ int run_group(davis_handle *h, Stage &stage, Group &g, int gi, const uint8_t *de
     vw.window_blocks = h->W;
     vw.stream0 = g.s0;
     vw.lut = h->d_lut;
+    vw.elem = h->elem;
+    const bool bytes_in = h->elem == 2;
 
     SearchParams sp;
     sp.pat_rev = h->pat_rev;
@@ -200,12 +203,13 @@ int run_group(davis_handle *h, Stage &stage, Group &g, int gi, const uint8_t *de
     CU(cudaMemsetAsync(stage.lost, 0, g.hit_cap, st));
     CU(cudaMemsetAsync(stage.marks, 0, sizeof(uint32_t) * (size_t)g.ns * stage.mark_words, st));
     CU(cudaEventRecord(g.ev[0], st));
-    launch_demod(vw, stage.planes, g.ns, stage.tiles, stage.words_alloc, nullptr, 0, st);
+    if (bytes_in) launch_demod(vw, stage.planes, g.ns, stage.tiles, stage.words_alloc, nullptr, 0, st);
+    else launch_exact_all(vw, sp, stage.planes, st);               // complex input: fp64 decisions throughout
     CU(cudaEventRecord(g.ev[1], st));
     launch_search(stage.planes, sp, stage.cand, stage.ctr, st);
     CU(cudaEventRecord(g.ev[2], st));
-    launch_precheck(vw, sp, stage.cand, stage.conf, stage.marks, stage.glist, stage.ctr, st);
-    launch_exact(vw, sp, stage.planes, stage.glist, stage.fixes, stage.ctr, st);
+    launch_precheck(vw, sp, stage.cand, stage.conf, stage.marks, stage.glist, stage.ctr, !bytes_in, st);
+    if (bytes_in) launch_exact(vw, sp, stage.planes, stage.glist, stage.fixes, stage.ctr, st);
     launch_slice(vw, sp, stage.planes, stage.conf, stage.fixes, stage.recs, stage.tbl, stage.lost,
                  stage.ctr, n_blocks, st);
     unsigned int *count = stage.per_stream, *start = count + g.ns, *fill = start + g.ns + 1;
@@ -216,7 +220,7 @@ int run_group(davis_handle *h, Stage &stage, Group &g, int gi, const uint8_t *de
     launch_carry(h->carry[h->cur] + (size_t)g.s0 * h->carry_stride,
                  h->carry[h->cur ^ 1] + (size_t)g.s0 * h->carry_stride, h->carry_stride, h->n_keep,
                  dev_input, input_stride, n_blocks * h->B, g.ns, h->d_blocks_done + g.s0, n_blocks,
-                 st);
+                 h->elem, st);
     CU(cudaEventRecord(g.ev[3], st));
     CU(cudaMemcpyAsync(&h->h_ctr[gi], stage.ctr, sizeof(Counters), cudaMemcpyDeviceToHost, st));
     CU(cudaEventRecord(g.ev[4], st));
@@ -345,14 +349,49 @@ int davis_reset(davis_handle *h, int stream) {
     return DAVIS_OK;
 }
 
-int davis_demod_u8(davis_handle *h, const uint8_t *iq, size_t bytes_per_stream,
-                   size_t stream_stride, int n_blocks, void *cuda_stream) {
+}  // extern "C"
+
+// The carried tail is kept in the input's own element type.  Changing the type is
+// allowed only on a fresh (or reset) handle: the reference keeps one complex128
+// buffer for both entries (dsp.py:129,144-151), this library keeps raw input.
+static int set_elem(davis_handle *h, int elem) {
+    if (h->elem == elem) return DAVIS_OK;
+    for (int64_t b : h->h_blocks_done)
+        if (b != 0)
+            return fail(h, DAVIS_E_STATE, "input type changed in mid-stream: davis_reset(h, -1) first");
+    CU(cudaSetDevice(h->device));
+    CU(cudaDeviceSynchronize());
+    const size_t stride = (size_t)elem * h->n_keep;
+    uint8_t *fresh[2] = {nullptr, nullptr};
+    for (int i = 0; i < 2; i++) {
+        if (cudaMalloc((void **)&fresh[i], stride * h->n_streams) != cudaSuccess) {
+            if (fresh[0]) cudaFree(fresh[0]);
+            cudaGetLastError();
+            return fail(h, DAVIS_E_NOMEM, "carry buffers for the new input type");
+        }
+        cudaMemset(fresh[i], 0, stride * h->n_streams);
+    }
+    for (int i = 0; i < 2; i++) { cudaFree(h->carry[i]); h->carry[i] = fresh[i]; }
+    h->carry_stride = stride;
+    h->elem = elem;
+    h->cur = 0;
+    return DAVIS_OK;
+}
+
+// Demodulator.demodulate for n_blocks blocks of every stream; `elem` = bytes per sample.
+static int demod_common(davis_handle *h, const uint8_t *iq, size_t bytes_per_stream,
+                        size_t stream_stride, int n_blocks, void *cuda_stream, int elem) {
     if (!h) return DAVIS_E_INVAL;
     if (!iq || n_blocks < 1) return fail(h, DAVIS_E_INVAL, "null input or n_blocks < 1");
     if (n_blocks > h->cfg.max_blocks)
         return fail(h, DAVIS_E_INVAL, "n_blocks exceeds davis_cfg.max_blocks");
-    if (bytes_per_stream != (size_t)n_blocks * 2 * h->B)
+    if (bytes_per_stream != (size_t)n_blocks * elem * h->B)
         return fail(h, DAVIS_E_SIZE, "Incompatible array sizes");
+    if (h->queued) return fail(h, DAVIS_E_STATE, "previous call not fetched");
+    {
+        const int rc_e = set_elem(h, elem);
+        if (rc_e) return rc_e;
+    }
     if (h->n_streams > 1 && stream_stride < bytes_per_stream)
         return fail(h, DAVIS_E_SIZE, "stream_stride smaller than bytes_per_stream");
     if (h->queued) return fail(h, DAVIS_E_STATE, "previous call not fetched");
@@ -437,8 +476,23 @@ int davis_demod_u8(davis_handle *h, const uint8_t *iq, size_t bytes_per_stream,
     return DAVIS_OK;
 }
 
-int davis_demod_c64(davis_handle *h, const float *, size_t, size_t, int, void *) {
-    return fail(h, DAVIS_E_INVAL, "complex64 input is not implemented yet");
+extern "C" {
+
+int davis_demod_u8(davis_handle *h, const uint8_t *iq, size_t bytes_per_stream,
+                   size_t stream_stride, int n_blocks, void *cuda_stream) {
+    return demod_common(h, iq, bytes_per_stream, stream_stride, n_blocks, cuda_stream, 2);
+}
+
+int davis_demod_c64(davis_handle *h, const float *iq, size_t samples_per_stream,
+                    size_t stream_stride_bytes, int n_blocks, void *cuda_stream) {
+    return demod_common(h, reinterpret_cast<const uint8_t *>(iq), samples_per_stream * 8,
+                        stream_stride_bytes, n_blocks, cuda_stream, 8);
+}
+
+int davis_demod_c128(davis_handle *h, const double *iq, size_t samples_per_stream,
+                     size_t stream_stride_bytes, int n_blocks, void *cuda_stream) {
+    return demod_common(h, reinterpret_cast<const uint8_t *>(iq), samples_per_stream * 16,
+                        stream_stride_bytes, n_blocks, cuda_stream, 16);
 }
 
 // Wait for the queued call and bring its packets into the pinned result buffer.
@@ -588,6 +642,7 @@ static int debug_view(davis_handle *h, View *vw) {
     vw->window_blocks = h->W;
     vw->stream0 = 0;
     vw->lut = h->d_lut;
+    vw->elem = h->elem;
     return DAVIS_OK;
 }
 
@@ -611,6 +666,7 @@ int davis_debug_disc(davis_handle *h, int stream, double *out, size_t cap) {
 int davis_debug_disc32(davis_handle *h, int stream, float *out, size_t cap) {
     if (!h || !out || stream < 0 || stream >= h->n_streams) return fail(h, DAVIS_E_INVAL, "bad argument");
     if (cap < (size_t)2 * h->B) return fail(h, DAVIS_E_OVERFLOW, "need 2*block_size floats");
+    if (h->elem != 2) return fail(h, DAVIS_E_INVAL, "the fp32 kernel exists for uint8 input only");
     if (h->queued) return fail(h, DAVIS_E_STATE, "fetch the call first");
     CU(cudaSetDevice(h->device));
     CU(cudaDeviceSynchronize());

@@ -48,6 +48,7 @@ struct View {
     int window_blocks;        // W = buffer_length / block_size
     int stream0;              // first stream of this pipeline stage (for records)
     const double *lut;        // device copy of the float64 byte->sample table (256 entries)
+    int elem;                 // bytes per sample: 2 (uint8 I,Q), 8 (complex64) or 16 (complex128)
 };
 
 // copy the table into shared memory (call from every thread of the block)
@@ -57,8 +58,8 @@ __device__ __forceinline__ void stage_lut(double *sm_lut, const double *lut) {
 }
 
 __device__ __forceinline__ const uint8_t *sample_ptr(const View &vw, int s, int v) {
-    return v < vw.n_carry ? vw.carry + (size_t)s * vw.carry_stride + 2 * (size_t)v
-                          : vw.input + (size_t)s * vw.input_stride + 2 * (size_t)(v - vw.n_carry);
+    return v < vw.n_carry ? vw.carry + (size_t)s * vw.carry_stride + vw.elem * (size_t)v
+                          : vw.input + (size_t)s * vw.input_stride + vw.elem * (size_t)(v - vw.n_carry);
 }
 
 __device__ __forceinline__ int64_t global_of(const View &vw, int s, int v) {
@@ -69,7 +70,7 @@ __device__ __forceinline__ int64_t global_of(const View &vw, int s, int v) {
 // fp64, reference order.  No FMA contraction anywhere (explicit _rn intrinsics).
 //
 // The evaluators are templated on a sample source `Src` with
-//     uchar2 at(int v) const      raw (I, Q) bytes of V index v (v >= 0)
+//     Cplx sample(lut, int v)     the unrotated sample of V index v (v >= 0)
 //     int64_t g0                  global sample index of v = 0
 // GlobalSrc reads the carry/input buffers directly; SpanSrc reads a span that a
 // warp staged in shared memory with coalesced 16-byte loads.
@@ -79,39 +80,62 @@ __device__ __forceinline__ int64_t global_of(const View &vw, int s, int v) {
 // ---------------------------------------------------------------------------
 struct Cplx { double re, im; };
 
-struct GlobalSrc {
+// One sample as the reference holds it in raw_samples (complex128, dsp.py:144-151):
+// the LUT value of the two bytes (ByteToCmplxLUT.execute, dsp.py:28-39), or the
+// complex input itself (dest[:] = input_data).  ES = bytes per sample.
+template <int ES>
+__device__ __forceinline__ Cplx load_sample(const double *lut, const uint8_t *p) {
+    if constexpr (ES == 2) {
+        const uchar2 u = *reinterpret_cast<const uchar2 *>(p);
+        return Cplx{lut[u.x], lut[u.y]};
+    } else if constexpr (ES == 8) {
+        const float2 f = *reinterpret_cast<const float2 *>(p);
+        return Cplx{(double)f.x, (double)f.y};
+    } else {
+        const double2 d = *reinterpret_cast<const double2 *>(p);
+        return Cplx{d.x, d.y};
+    }
+}
+
+template <int ES>
+struct GlobalSrcT {
+    static constexpr int elem_bytes = ES;
     const uint8_t *carry, *input;
     int n_carry;
     int64_t g0;
-    __device__ __forceinline__ GlobalSrc(const View &vw, int s)
+    __device__ __forceinline__ GlobalSrcT(const View &vw, int s)
         : carry(vw.carry + (size_t)s * vw.carry_stride),
           input(vw.input + (size_t)s * vw.input_stride),
           n_carry(vw.n_carry),
           g0(vw.blocks_done[s] * (int64_t)vw.block - vw.n_carry) {}
-    __device__ __forceinline__ uchar2 at(int v) const {
-        const uint8_t *p = v < n_carry ? carry + 2 * (size_t)v : input + 2 * (size_t)(v - n_carry);
-        return *reinterpret_cast<const uchar2 *>(p);
+    __device__ __forceinline__ Cplx sample(const double *lut, int v) const {
+        return load_sample<ES>(lut, v < n_carry ? carry + ES * (size_t)v : input + ES * (size_t)(v - n_carry));
     }
 };
+using GlobalSrc = GlobalSrcT<2>;
 
-struct SpanSrc {
+template <int ES>
+struct SpanSrcT {
+    static constexpr int elem_bytes = ES;
     const uint8_t *base;      // shared memory; byte 0 holds V index v0
     int v0;
     int64_t g0;
-    __device__ __forceinline__ uchar2 at(int v) const {
-        return *reinterpret_cast<const uchar2 *>(base + 2 * (v - v0));
+    __device__ __forceinline__ Cplx sample(const double *lut, int v) const {
+        return load_sample<ES>(lut, base + ES * (v - v0));
     }
 };
+using SpanSrc = SpanSrcT<2>;
 
 // A warp copies V samples [v_begin, v_begin + n) of stream s into `dst` (shared,
-// 16-byte aligned, room for 2*n + 32 bytes) and returns the source describing it.
+// 16-byte aligned, room for ES*n + 32 bytes) and returns the source describing it.
 // Chunks before the start of V are zero-filled (they are only ever addressed for
 // g < 0, where the evaluators substitute the zero history anyway).
-__device__ __forceinline__ SpanSrc stage_span(const View &vw, int s, int v_begin, int n,
-                                              uint8_t *dst, int lane) {
-    const long long b0 = (2LL * v_begin) & ~15LL;              // floor to a 16-byte chunk
-    const long long b1 = 2LL * (v_begin + n);
-    const long long carry_bytes = 2LL * vw.n_carry, total = carry_bytes + 2LL * vw.n_new;
+template <int ES>
+__device__ __forceinline__ SpanSrcT<ES> stage_span(const View &vw, int s, int v_begin, int n,
+                                                   uint8_t *dst, int lane) {
+    const long long b0 = ((long long)ES * v_begin) & ~15LL;    // floor to a 16-byte chunk
+    const long long b1 = (long long)ES * (v_begin + n);
+    const long long carry_bytes = (long long)ES * vw.n_carry, total = carry_bytes + (long long)ES * vw.n_new;
     const uint8_t *carry = vw.carry + (size_t)s * vw.carry_stride;
     const uint8_t *input = vw.input + (size_t)s * vw.input_stride;
     const int chunks = (int)((b1 - b0 + 15) >> 4);
@@ -124,9 +148,10 @@ __device__ __forceinline__ SpanSrc stage_span(const View &vw, int s, int v_begin
         reinterpret_cast<uint4 *>(dst)[c] = val;
     }
     __syncwarp();
-    SpanSrc src;
+    SpanSrcT<ES> src;
     src.base = dst;
-    src.v0 = (int)(b0 >> 1);
+    // v0 may be fractional for ES = 16 only if b0 is not a multiple of ES: it always is
+    src.v0 = (int)(b0 / ES);
     src.g0 = vw.blocks_done[s] * (int64_t)vw.block - vw.n_carry;
     return src;
 }
@@ -164,9 +189,9 @@ __device__ __forceinline__ Cplx exact_rotated(const double *lut, const Src &src,
     Cplx r{0.0, 0.0};
     const int64_t g = src.g0 + v;
     if (g < 0 || v < 0) return r;
-    const uchar2 u = src.at(v);
-    const double xr = lut[u.x];
-    const double xi = lut[u.y];
+    const Cplx x = src.sample(lut, v);
+    const double xr = x.re;
+    const double xi = x.im;
     switch ((int)(g & 3)) {
     case 0: r.re = xr;  r.im = xi;  break;
     case 1: r.re = -xi; r.im = xr;  break;
@@ -231,8 +256,8 @@ __device__ __forceinline__ Cplx fixed_rotated(double x, double y) {
 template <int K, int N, class Src>
 struct FixedWindow {
     static __device__ __forceinline__ void run(const double *lut, const Src &src, int v, Cplx (&r)[N]) {
-        const uchar2 u = src.at(v + K);
-        r[K] = fixed_rotated<K>(lut[u.x], lut[u.y]);
+        const Cplx x = src.sample(lut, v + K);
+        r[K] = fixed_rotated<K>(x.re, x.im);
         FixedWindow<K + 1, N, Src>::run(lut, src, v, r);
     }
 };
@@ -268,8 +293,12 @@ __device__ __forceinline__ void fixed_filtered_run(const double *lut, const Src 
 template <int NF, class Src>
 __device__ __forceinline__ void filtered_run(const double *lut, const Src &src, int v_first,
                                              Cplx (&F)[NF]) {
-    if (v_first - 9 >= 0 && src.g0 + v_first - 9 >= 0) fixed_filtered_run<NF>(lut, src, v_first, F);
-    else exact_filtered_run<NF>(lut, src, v_first, F);
+    // byte input only: the LUT never yields a zero, so no signed zero can make the two
+    // forms differ; complex input (which may hold exact zeros) keeps the reference phase
+    if (Src::elem_bytes == 2 && v_first - 9 >= 0 && src.g0 + v_first - 9 >= 0)
+        fixed_filtered_run<NF>(lut, src, v_first, F);
+    else
+        exact_filtered_run<NF>(lut, src, v_first, F);
 }
 
 // numerator of D[g]: Im a * Re b - Re a * Im b,  a = F[g-1], b = F[g]

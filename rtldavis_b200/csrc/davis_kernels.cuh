@@ -71,7 +71,9 @@ void launch_demod(const View &vw, uint32_t *words, int n_streams, int tiles, int
 void launch_search(const uint32_t *planes, const SearchParams &sp, Cand *cand, Counters *ctr,
                    cudaStream_t st);
 void launch_precheck(const View &vw, const SearchParams &sp, const Cand *cand, Cand *conf,
-                     uint32_t *marks, uint2 *glist, Counters *ctr, cudaStream_t st);
+                     uint32_t *marks, uint2 *glist, Counters *ctr, bool bitmap_is_exact,
+                     cudaStream_t st);
+void launch_exact_all(const View &vw, const SearchParams &sp, uint32_t *planes, cudaStream_t st);
 void launch_exact(const View &vw, const SearchParams &sp, uint32_t *planes, const uint2 *glist,
                   Fix *fixes, Counters *ctr, cudaStream_t st);
 void launch_slice(const View &vw, const SearchParams &sp, const uint32_t *planes,
@@ -84,7 +86,7 @@ void launch_order(const davis_hit *tmp, const Counters *ctr, int stream0, int n_
                   unsigned int *bucket, davis_hit *out, cudaStream_t st);
 void launch_carry(const uint8_t *carry_old, uint8_t *carry_new, size_t carry_stride, int keep,
                   const uint8_t *input, size_t input_stride, int n_new, int n_streams,
-                  int64_t *blocks_done, int n_blocks, cudaStream_t st);
+                  int64_t *blocks_done, int n_blocks, int elem, cudaStream_t st);
 void launch_exact_disc(const View &vw, int stream, int v0, int n, double *out, cudaStream_t st);
 void launch_crc16(const uint8_t *data, size_t n, size_t len, uint16_t init, uint16_t poly,
                   int swap_bits, uint16_t *out, cudaStream_t st);

@@ -210,7 +210,8 @@ void launch_search(const uint32_t *words, const SearchParams &sp, Cand *cand, Co
 // ---------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
 k_precheck(View vw, SearchParams sp, const Cand *__restrict__ cand, Cand *__restrict__ conf,
-           uint32_t *__restrict__ marks, uint2 *__restrict__ glist, Counters *ctr) {
+           uint32_t *__restrict__ marks, uint2 *__restrict__ glist, Counters *ctr,
+           int bitmap_is_exact) {
     __shared__ double lut[256];
     stage_lut(lut, vw.lut);
     const unsigned int n = min(ctr->n_cand, sp.cand_cap);
@@ -225,7 +226,7 @@ k_precheck(View vw, SearchParams sp, const Cand *__restrict__ cand, Cand *__rest
         if (i < n) {
             c = cand[i];
             pass = c.miss < 0;
-            if (!pass) {
+            if (!pass && !bitmap_is_exact) {
                 const uint32_t want = (sp.pat_rev >> c.miss) & 1u;
                 pass = exact_bit(lut, GlobalSrc(vw, (int)c.stream), c.v + SPS * c.miss) == want;
             }
@@ -243,7 +244,7 @@ k_precheck(View vw, SearchParams sp, const Cand *__restrict__ cand, Cand *__rest
         // groups this position needs that nobody queued yet
         unsigned int fresh[8];
         int n_fresh = 0;
-        if (pass) {
+        if (pass && !bitmap_is_exact) {
             const int g0 = c.v / GROUP_SAMPLES, g1 = (c.v + SPS * (PKT_SYMS - 1)) / GROUP_SAMPLES;
             uint32_t *row = marks + (size_t)c.stream * sp.mark_words;
             for (int g = g0; g <= g1; g++) {
@@ -272,8 +273,9 @@ k_precheck(View vw, SearchParams sp, const Cand *__restrict__ cand, Cand *__rest
 }
 
 void launch_precheck(const View &vw, const SearchParams &sp, const Cand *cand, Cand *conf,
-                     uint32_t *marks, uint2 *glist, Counters *ctr, cudaStream_t st) {
-    k_precheck<<<148 * 4, 256, 0, st>>>(vw, sp, cand, conf, marks, glist, ctr);
+                     uint32_t *marks, uint2 *glist, Counters *ctr, bool bitmap_is_exact,
+                     cudaStream_t st) {
+    k_precheck<<<148 * 4, 256, 0, st>>>(vw, sp, cand, conf, marks, glist, ctr, bitmap_is_exact ? 1 : 0);
 }
 
 // ---------------------------------------------------------------------------
@@ -415,6 +417,49 @@ __device__ void dedupe_insert(const Rec *recs, uint32_t id, uint32_t *tbl, uint3
 }
 
 // ---------------------------------------------------------------------------
+// k_exact_all: the complex-input entry (dsp.py:144-150: dest[:] = input_data).  There is
+// no fp32 streaming form for arbitrary complex samples; the whole bitmap is decided in
+// fp64 in the reference's operation order (reference-phase form), one warp per group of
+// 224 samples, and the search then runs on exact bits.  The live rate of this entry is
+// one SDR (268.8 kS/s); it is built for identity with the reference, not for speed.
+// ---------------------------------------------------------------------------
+template <int ES>
+__global__ void __launch_bounds__(EXACT_WARPS * 32)
+k_exact_all(View vw, SearchParams sp, uint32_t *__restrict__ planes, int groups) {
+    constexpr int SPAN = GROUP_SAMPLES + 10;
+    __shared__ double lut[256];
+    __shared__ uint4 span_mem[EXACT_WARPS][(ES * SPAN + 32 + 15) / 16];
+    stage_lut(lut, vw.lut);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const long long n = (long long)sp.n_streams * groups;
+    for (long long gi = (long long)blockIdx.x * EXACT_WARPS + warp; gi < n;
+         gi += (long long)gridDim.x * EXACT_WARPS) {
+        const int s = (int)(gi / groups), grp = (int)(gi - (long long)s * groups);
+        __syncwarp();
+        const SpanSrcT<ES> src = stage_span<ES>(vw, s, grp * GROUP_SAMPLES - 10, SPAN,
+                                                reinterpret_cast<uint8_t *>(span_mem[warp]), lane);
+        const int n0 = grp * GROUP_SAMPLES + GRP_LANE * lane;
+        uint32_t bits = 0;
+#pragma unroll 1
+        for (int t = 0; t < GRP_LANE; t++) bits |= exact_bit(lut, src, n0 + t) << t;
+        uint32_t word = bits << (GRP_LANE * (lane & 3));
+        word |= __shfl_xor_sync(0xFFFFFFFFu, word, 1);
+        word |= __shfl_xor_sync(0xFFFFFFFFu, word, 2);
+        const int wi = grp * GROUP_WORDS + (lane >> 2);
+        if ((lane & 3) == 0 && wi < sp.words_alloc) planes[(size_t)s * sp.words_alloc + wi] = word;
+    }
+}
+
+void launch_exact_all(const View &vw, const SearchParams &sp, uint32_t *planes, cudaStream_t st) {
+    const int groups = (sp.words_alloc + GROUP_WORDS - 1) / GROUP_WORDS;
+    const long long n = (long long)sp.n_streams * groups;
+    const unsigned grid = (unsigned)std::min<long long>((n + EXACT_WARPS - 1) / EXACT_WARPS, 148LL * 8);
+    if (!grid) return;
+    if (vw.elem == 8) k_exact_all<8><<<grid, EXACT_WARPS * 32, 0, st>>>(vw, sp, planes, groups);
+    else k_exact_all<16><<<grid, EXACT_WARPS * 32, 0, st>>>(vw, sp, planes, groups);
+}
+
+// ---------------------------------------------------------------------------
 // k_slice: one thread per surviving candidate, after k_exact has replaced the
 // decisions it needs by the reference's float64 ones.  The 80 symbols are read
 // from the bitmap (symbol i of position 28w + b: bit b of word w + i/2 for even i,
@@ -529,13 +574,12 @@ void launch_slice(const View &vw, const SearchParams &sp, const uint32_t *planes
 // one-block `filtered` buffer indexed by two-block window positions) and the
 // discriminator mean Parser.parse takes (protocol.py:304-310), all in fp64.
 // ---------------------------------------------------------------------------
-constexpr int CONFIRM_WARPS = 8;
-
 // sum of |F|^2 over V indices [v0, v1), v1 - v0 <= 32 * FIN_CHUNK; lane l takes the
 // FIN_CHUNK consecutive positions starting at v0 + FIN_CHUNK * l
 constexpr int FIN_CHUNK = 7;                                   // 224 / 32
 
-__device__ double power_sum(const double *lut, const SpanSrc &src, int v0, int v1, int lane) {
+template <class Src>
+__device__ double power_sum(const double *lut, const Src &src, int v0, int v1, int lane) {
     double acc = 0.0;
     const int a = v0 + FIN_CHUNK * lane;
     if (a < v1) {
@@ -549,7 +593,8 @@ __device__ double power_sum(const double *lut, const SpanSrc &src, int v0, int v
 }
 
 // sum of D[v] over [v0, v0 + 32 * FIN_CHUNK)
-__device__ double disc_sum(const double *lut, const SpanSrc &src, int v0, int lane) {
+template <class Src>
+__device__ double disc_sum(const double *lut, const Src &src, int v0, int lane) {
     const int a = v0 + FIN_CHUNK * lane;
     Cplx F[FIN_CHUNK + 1];
     filtered_run<FIN_CHUNK + 1>(lut, src, a - 1, F);
@@ -560,7 +605,8 @@ __device__ double disc_sum(const double *lut, const SpanSrc &src, int v0, int la
     return warp_sum(acc);
 }
 
-__global__ void __launch_bounds__(CONFIRM_WARPS * 32)
+template <int ES, int WARPS>
+__global__ void __launch_bounds__(WARPS * 32)
 k_finalize(View vw, SearchParams sp, const Rec *__restrict__ recs,
            const uint8_t *__restrict__ lost, davis_hit *__restrict__ hits,
            unsigned int *__restrict__ per_stream, Counters *ctr) {
@@ -568,13 +614,13 @@ k_finalize(View vw, SearchParams sp, const Rec *__restrict__ recs,
     constexpr int SPAN_P = 2 * PRE + 32, SPAN_D = PRE + 32;  // + FIR history + chunk overrun
     static_assert(PRE == 32 * FIN_CHUNK, "one chunk per lane");
     __shared__ double lut[256];
-    __shared__ uint4 mem_p[CONFIRM_WARPS][(2 * SPAN_P + 32 + 15) / 16];
-    __shared__ uint4 mem_d[CONFIRM_WARPS][(2 * SPAN_D + 32 + 15) / 16];
+    __shared__ uint4 mem_p[WARPS][(ES * SPAN_P + 32 + 15) / 16];
+    __shared__ uint4 mem_d[WARPS][(ES * SPAN_D + 32 + 15) / 16];
     stage_lut(lut, vw.lut);
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const unsigned int n = min(ctr->n_rec, sp.hit_cap);
-    const unsigned int warps = gridDim.x * CONFIRM_WARPS;
-    for (unsigned int ri = blockIdx.x * CONFIRM_WARPS + warp; ri < n; ri += warps) {
+    const unsigned int warps = gridDim.x * WARPS;
+    for (unsigned int ri = blockIdx.x * WARPS + warp; ri < n; ri += warps) {
         if (lost[ri]) continue;
         const Rec r = recs[ri];
         const int s = (int)r.stream;
@@ -589,12 +635,12 @@ k_finalize(View vw, SearchParams sp, const Rec *__restrict__ recs,
         const int s1 = min(q + PRE, B + 1);                    // slice end is clipped by numpy
         const int n0 = max(0, q - PRE);
         __syncwarp();
-        const SpanSrc sp_p = stage_span(vw, s, f0 + n0 - 10, s1 - n0 + 10,
+        const SpanSrcT<ES> sp_p = stage_span<ES>(vw, s, f0 + n0 - 10, s1 - n0 + 10,
                                         reinterpret_cast<uint8_t *>(mem_p[warp]), lane);
         // protocol.py:304-310: discriminated[] spans the window's last two blocks;
         // discriminated[i] = D[(call-1)*B + i], V index w0 + (W-2)*B + i.
         const int d0 = w0 + (vw.window_blocks - 2) * B + q;
-        const SpanSrc sp_d = stage_span(vw, s, d0 - 11, PRE + 11,
+        const SpanSrcT<ES> sp_d = stage_span<ES>(vw, s, d0 - 11, PRE + 11,
                                         reinterpret_cast<uint8_t *>(mem_d[warp]), lane);
         const double sig = power_sum(lut, sp_p, f0 + q, f0 + s1, lane) / (double)(s1 - q);
         const double noise = q > n0 ? power_sum(lut, sp_p, f0 + n0, f0 + q, lane) / (double)(q - n0)
@@ -622,7 +668,13 @@ k_finalize(View vw, SearchParams sp, const Rec *__restrict__ recs,
 
 void launch_finalize(const View &vw, const SearchParams &sp, const Rec *recs, const uint8_t *lost,
                      davis_hit *hits, unsigned int *per_stream, Counters *ctr, cudaStream_t st) {
-    k_finalize<<<148 * 4, CONFIRM_WARPS * 32, 0, st>>>(vw, sp, recs, lost, hits, per_stream, ctr);
+    // fewer warps per CTA for the wider element types: the staged spans share 48 KiB
+    if (vw.elem == 2)
+        k_finalize<2, 8><<<148 * 4, 8 * 32, 0, st>>>(vw, sp, recs, lost, hits, per_stream, ctr);
+    else if (vw.elem == 8)
+        k_finalize<8, 4><<<148 * 4, 4 * 32, 0, st>>>(vw, sp, recs, lost, hits, per_stream, ctr);
+    else
+        k_finalize<16, 2><<<148 * 4, 2 * 32, 0, st>>>(vw, sp, recs, lost, hits, per_stream, ctr);
 }
 
 // ---------------------------------------------------------------------------
@@ -737,9 +789,9 @@ void launch_order(const davis_hit *tmp, const Counters *ctr, int stream0, int n_
 __global__ void __launch_bounds__(256)
 k_carry(const uint8_t *__restrict__ carry_old, uint8_t *__restrict__ carry_new,
         size_t carry_stride, int keep, const uint8_t *__restrict__ input, size_t input_stride,
-        int n_new, int64_t *blocks_done, int n_blocks) {
+        int n_new, int64_t *blocks_done, int n_blocks, int elem) {
     const int s = blockIdx.y;
-    const long long keep_b = 2LL * keep, new_b = 2LL * n_new;
+    const long long keep_b = (long long)elem * keep, new_b = (long long)elem * n_new;
     const long long chunks = keep_b / 16;
     for (long long c = (long long)blockIdx.x * blockDim.x + threadIdx.x; c < chunks;
          c += (long long)gridDim.x * blockDim.x) {
@@ -755,30 +807,34 @@ k_carry(const uint8_t *__restrict__ carry_old, uint8_t *__restrict__ carry_new,
 
 void launch_carry(const uint8_t *carry_old, uint8_t *carry_new, size_t carry_stride, int keep,
                   const uint8_t *input, size_t input_stride, int n_new, int n_streams,
-                  int64_t *blocks_done, int n_blocks, cudaStream_t st) {
-    const long long chunks = 2LL * keep / 16;
-    int gx = (int)min((chunks + 255) / 256, 8LL);
+                  int64_t *blocks_done, int n_blocks, int elem, cudaStream_t st) {
+    const long long chunks = (long long)elem * keep / 16;
+    int gx = (int)min((chunks + 255) / 256, 32LL);
     for (int s0 = 0; s0 < n_streams; s0 += 65535) {
         const int ns = min(65535, n_streams - s0);
         k_carry<<<dim3(gx, ns), 256, 0, st>>>(
             carry_old + (size_t)s0 * carry_stride, carry_new + (size_t)s0 * carry_stride,
             carry_stride, keep, input + (size_t)s0 * input_stride, input_stride, n_new,
-            blocks_done + s0, n_blocks);
+            blocks_done + s0, n_blocks, elem);
     }
 }
 
 // ---------------------------------------------------------------------------
 // debug / parity taps
 // ---------------------------------------------------------------------------
+template <int ES>
 __global__ void k_exact_disc(View vw, int stream, int v0, int n, double *out) {
     __shared__ double lut[256];
     stage_lut(lut, vw.lut);
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) out[i] = exact_disc(lut, GlobalSrc(vw, stream), v0 + i);
+    if (i < n) out[i] = exact_disc(lut, GlobalSrcT<ES>(vw, stream), v0 + i);
 }
 
 void launch_exact_disc(const View &vw, int stream, int v0, int n, double *out, cudaStream_t st) {
-    if (n > 0) k_exact_disc<<<(n + 255) / 256, 256, 0, st>>>(vw, stream, v0, n, out);
+    if (n <= 0) return;
+    if (vw.elem == 2) k_exact_disc<2><<<(n + 255) / 256, 256, 0, st>>>(vw, stream, v0, n, out);
+    else if (vw.elem == 8) k_exact_disc<8><<<(n + 255) / 256, 256, 0, st>>>(vw, stream, v0, n, out);
+    else k_exact_disc<16><<<(n + 255) / 256, 256, 0, st>>>(vw, stream, v0, n, out);
 }
 
 // CRC.checksum for arbitrary (init, poly) with a shared-memory table built as

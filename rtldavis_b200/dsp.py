@@ -146,8 +146,10 @@ class BatchDemodulator:
             nbytes = shape[1]
         else:
             iq = np.asarray(iq)
+            if np.iscomplexobj(iq):                        # dsp.py:144-151: dest[:] = input_data
+                return self._submit_complex(iq, cuda_stream)
             if iq.dtype != np.uint8:
-                raise TypeError("input must be uint8 interleaved I/Q")
+                raise TypeError("input must be uint8 interleaved I/Q or complex")
             if iq.ndim == 1:
                 iq = iq[None, :]
             if iq.ndim != 2 or iq.shape[0] != self.n_streams:
@@ -163,6 +165,33 @@ class BatchDemodulator:
         self._keepalive = iq
         rc = self._L.davis_demod_u8(self._h, ptr, nbytes, stride, n_blocks,
                                     C.c_void_p(cuda_stream) if cuda_stream else None)
+        if rc != 0:
+            self._keepalive = None
+        check(rc, self._h)
+        self._last_blocks = n_blocks
+
+    def _submit_complex(self, iq: np.ndarray, cuda_stream: Optional[int]) -> None:
+        """Complex host input: complex64 stays complex64, everything else becomes
+        complex128 (the type the reference's raw_samples buffer has)."""
+        B = self.cfg.block_size
+        if iq.dtype != np.complex64:
+            iq = iq.astype(np.complex128, copy=False)
+        if iq.ndim == 1:
+            iq = iq[None, :]
+        if iq.ndim != 2 or iq.shape[0] != self.n_streams:
+            raise ValueError("Incompatible array sizes")
+        if iq.strides[1] != iq.itemsize:
+            iq = np.ascontiguousarray(iq)
+        n = iq.shape[1]
+        if n == 0 or n % B:
+            raise ValueError("Incompatible array sizes")
+        n_blocks = n // B
+        if n_blocks > self.max_blocks:
+            raise ValueError(f"{n_blocks} blocks per call exceed max_blocks={self.max_blocks}")
+        fn = self._L.davis_demod_c64 if iq.dtype == np.complex64 else self._L.davis_demod_c128
+        self._keepalive = iq
+        rc = fn(self._h, iq.ctypes.data, n, iq.strides[0], n_blocks,
+                C.c_void_p(cuda_stream) if cuda_stream else None)
         if rc != 0:
             self._keepalive = None
         check(rc, self._h)
@@ -232,10 +261,13 @@ class Demodulator:
     def demodulate(self, input_data: np.ndarray) -> List[Packet]:
         arr = np.asarray(input_data)
         if np.iscomplexobj(arr):
-            raise NotImplementedError("complex input is not wired to the GPU path yet")
-        if arr.size != 2 * self.cfg.block_size:              # dsp.py:32-36
-            raise ValueError("Incompatible array sizes")
-        self._batch.submit(arr.reshape(1, -1).astype(np.uint8, copy=False))
+            if arr.size != self.cfg.block_size:                  # dsp.py:145-149
+                raise ValueError("Incompatible array sizes")
+            self._batch.submit(arr.reshape(1, -1))
+        else:
+            if arr.size != 2 * self.cfg.block_size:              # dsp.py:32-36
+                raise ValueError("Incompatible array sizes")
+            self._batch.submit(arr.reshape(1, -1).astype(np.uint8, copy=False))
         self._last_hits = self._batch.fetch()
         return [Packet(int(h["index"]), h["data"].copy(), float(h["rssi"]), float(h["snr"]))
                 for h in self._last_hits]

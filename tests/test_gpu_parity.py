@@ -387,3 +387,78 @@ def test_snr_sweep_matches_oracle_per_snr(dsp, protocol):
         recovered[snr] = sum(p in valid for p in sent) / len(sent)
     assert all(recovered[s] == 1.0 for s in snrs if s >= 14), recovered
     assert all(recovered[s] == 0.0 for s in snrs if s <= 4), recovered
+
+
+# ---------------------------------------------------------------------------
+# complex input (dsp.py:144-151), the live pyrtlsdr entry
+# ---------------------------------------------------------------------------
+def test_complex64_golden_fixture(dsp):
+    """The reference was fed complex64 blocks for this fixture (gen_golden.py)."""
+    g = load_golden("complex_in_8192")
+    B = int(g["block"])
+    dem = dsp.Demodulator(_cfg(dsp, B))
+    iq = g["iq"]
+    got, rssi, snr = [], [], []
+    for k in range(iq.size // (2 * B)):
+        blk = O.bytes_to_complex(iq[2 * B * k:2 * B * (k + 1)]).astype(np.complex64)
+        pk = dem.demodulate(blk)
+        for p, h in zip(pk, dem.last_hits):
+            got.append((k, p.index, p.data.tobytes(), bool(h["crc_ok"])))
+            rssi.append(p.rssi)
+            snr.append(p.snr)
+    assert got == golden_rows(g)
+    np.testing.assert_allclose(rssi, g["pk_rssi"], rtol=0, atol=1e-9)
+    np.testing.assert_allclose(snr, g["pk_snr"], rtol=0, atol=1e-9)
+    dem.close()
+
+
+@pytest.mark.parametrize("dtype", [np.complex64, np.complex128])
+def test_complex_input_pyrtlsdr_scaling_matches_oracle(dsp, dtype):
+    """pyrtlsdr hands out (u / 127.5 - 1) as complex128, not the LUT's values: the
+    complex entry must use the samples as they are.  Block by block against the
+    oracle's complex path, then the same stream in multi-block calls."""
+    g = load_golden("hi_snr_8192")
+    B = int(g["block"])
+    n = 12
+    u = g["iq"][: 2 * B * n].astype(np.float64)
+    x = ((u[0::2] / 127.5 - 1.0) + 1j * (u[1::2] / 127.5 - 1.0)).astype(dtype)
+    orc = O.CallOracle(O.OracleConfig())
+    want, want_pow = [], []
+    for k in range(n):
+        for p in orc.demodulate(x[B * k:B * (k + 1)]):
+            want.append((k, p.index, p.data, bool(p.crc_ok)))
+            want_pow.append((p.rssi, p.snr))
+    assert len(want) >= 4
+    dem = dsp.Demodulator(_cfg(dsp, B))
+    got, got_pow = [], []
+    for k in range(n):
+        pk = dem.demodulate(x[B * k:B * (k + 1)])
+        for p, h in zip(pk, dem.last_hits):
+            got.append((k, p.index, p.data.tobytes(), bool(h["crc_ok"])))
+            got_pow.append((p.rssi, p.snr))
+    assert got == want
+    np.testing.assert_allclose(np.array(got_pow), np.array(want_pow), rtol=0, atol=1e-9)
+    d = dem.discriminated
+    assert np.all(np.abs(d - orc.discriminated) <= 1e-12 * np.maximum(np.abs(orc.discriminated), 1.0))
+    dem.close()
+    bd = dsp.BatchDemodulator(_cfg(dsp, B), 1, max_blocks=5)
+    rows, at = [], 0
+    for take in (5, 1, 4, 2):
+        bd.submit(x[B * at:B * (at + take)].reshape(1, -1))
+        rows += _rows(bd.fetch())
+        at += take
+    assert at == n and rows == want
+    bd.close()
+
+
+def test_input_type_change_needs_reset(dsp):
+    B = 8192
+    dem = dsp.Demodulator(_cfg(dsp, B))
+    dem.demodulate(np.full(2 * B, 127, dtype=np.uint8))
+    with pytest.raises(Exception):
+        dem.demodulate(np.zeros(B, dtype=np.complex128))
+    dem.reset()
+    assert dem.demodulate(np.zeros(B, dtype=np.complex128)) == []
+    with pytest.raises(ValueError):
+        dem.demodulate(np.zeros(B - 1, dtype=np.complex64))
+    dem.close()
