@@ -31,3 +31,29 @@ def crc_gate(hits: np.ndarray) -> List[Tuple[bytes, bool]]:
     payload (protocol.py:293-295) is implied by the library's dedupe on the
     unswapped payload (a bijection)."""
     return [(bytes(swap_bit_order(x) for x in h["data"]), bool(h["crc_ok"])) for h in hits]
+
+
+def parse_hits(hits: np.ndarray, cfg: dsp.PacketConfig, station_id=None) -> List[dict]:
+    """The part of ``Parser.parse`` (src/rtldavis/protocol.py:282-332) that sits on the
+    demodulation path, for a whole batch of records: bit-order swap, CRC gate, the
+    frequency error ``-int(mean(discriminated[index:index+224]) * Fs / 2 pi)``
+    (protocol.py:304-311; the mean comes from the device, ``davis_hit.disc_mean``),
+    message id and the station filter (protocol.py:325-329).  Hop bookkeeping and sensor
+    decoding (protocol.py:316-323,331) stay with the reference's Parser; each returned
+    dict carries what ``_parse_sensor_data`` needs (``data`` = the 8 message bytes,
+    ``rssi``, ``snr``) plus ``stream`` and ``call``."""
+    import math
+    out: List[dict] = []
+    for h in hits:
+        if not h["crc_ok"]:
+            continue
+        data = bytes(swap_bit_order(x) for x in h["data"])
+        msg = data[2:]
+        msg_id = msg[0] & 0x7
+        if station_id is not None and msg_id != station_id:
+            continue
+        freq_err = -int((float(h["disc_mean"]) * float(cfg.sample_rate)) / (2 * math.pi))
+        out.append({"stream": int(h["stream"]), "call": int(h["call"]), "index": int(h["index"]),
+                    "data": msg, "id": msg_id, "freq_err": freq_err,
+                    "rssi": float(h["rssi"]), "snr": float(h["snr"])})
+    return out
