@@ -280,22 +280,114 @@ void launch_precheck(const View &vw, const SearchParams &sp, const Cand *cand, C
 
 // ---------------------------------------------------------------------------
 // k_exact: one warp per queued group of GROUP_WORDS bitmap words (224 samples).
-// The group's decisions are recomputed in fp64 in the reference's operation order
-// and written over the fp32 ones, so everything downstream (sync check, slicing,
-// CRC) reads the reference's own bits.  Lane l decides the 7 samples
-// 224 g + 7 l .. + 6 from a register window of 16 samples (8 filter outputs).
-//
-// The rotation phase is taken relative to the lane's window: multiplying every
-// sample by the same power of j maps (F[n-1], F[n]) to (j^p F[n-1], j^p F[n]), each
-// component to +- a component (exactly: rounding is symmetric), and the cross
-// product im*re' - re*im' to the same two products in the same roles.  Only the
-// zero history of a fresh stream breaks that, and those groups take the generic
-// path (exact_bit).
+// The group's decisions are re-derived so that they provably equal the reference's
+// float64 sign bits, and written over the streaming kernel's, so everything downstream
+// (sync check, slicing, CRC) reads the reference's own bits.  Lane l decides the 7
+// samples 224 g + 7 l .. + 6 from a register window of 16 samples (8 filter outputs):
+// in fp32 with an error bound (guarded_bits below); a sample whose numerator lies
+// inside the bound -- a few in 10^5 -- is decided by the fp64 reference-phase form
+// (exact_bit), as is every sample of a group within reach of a fresh stream's zero
+// history.  (The previous version recomputed all 224 decisions in fp64 from the
+// shared-memory LUT: 0.67 ms per step against 0.2 ms.)
 // ---------------------------------------------------------------------------
 constexpr int EXACT_WARPS = 8;
 constexpr int GRP_LANE = GROUP_SAMPLES / 32;                   // 7 decisions per lane
 
-__global__ void __launch_bounds__(EXACT_WARPS * 32)
+// ---------------------------------------------------------------------------
+// Guarded fp32 decisions.  The numerator of D[n] (dsp.py:88) is evaluated in fp32 from
+// the integer-valued samples u - 127 (exact), the -0.4 of the LUT offset folded into a
+// period-4 constant as in k_demod, with an error bound evaluated beside it:
+//   |F32 - F| <= 6 * 2^-24 * (sum_m c[m] |u - 127| + 0.4) <= 4.6e-5 per component
+//     (five rounded FMAs, fp32 taps; pair sums of integers are exact), and
+//   |num32 - num| <= 4.6e-5 * S1 + 2^-23 * S2,  S1 = |re a| + |im a| + |re b| + |im b|,
+//     S2 = |im a * re b| + |re a * im b|   (one rounded product, one rounded FMA).
+// A sample whose |num32| exceeds tau = 1e-4 * S1 + 2^-22 * S2 + 1e-6 (more than twice
+// that bound) has the sign of the real-number numerator by a margin of > 1e-6 in these
+// units (6e-11 in the reference's), which is ~1e5 times the rounding error of the
+// reference's float64 evaluation in any summation order: its sign bit IS the
+// reference's.  Samples inside the band are reported in `unsure` and decided by the
+// fp64 reference-phase form.  `win` points at sample n0 - 10 of the staged span (2-byte
+// aligned shared memory); bit t of the result decides sample n0 + t, t < 7.  The
+// rotation phase is relative to the window (a common power of j cancels in the cross
+// product of two outputs).
+// ---------------------------------------------------------------------------
+__host__ __device__ constexpr float guard_residual(int k, int comp) {
+    const double c[9] = {DAVIS_C0, DAVIS_C1, DAVIS_C2, DAVIS_C3, DAVIS_C4,
+                         DAVIS_C3, DAVIS_C2, DAVIS_C1, DAVIS_C0};
+    const double sre[4] = {-0.4, 0.4, 0.4, -0.4}, sim[4] = {-0.4, -0.4, 0.4, 0.4};
+    double acc = 0.0;
+    for (int m = 0; m < 9; m++) acc += c[m] * (comp ? sim[(k + m) & 3] : sre[(k + m) & 3]);
+    return (float)acc;
+}
+
+__device__ __forceinline__ uint32_t guarded_bits(const uint8_t *win, uint32_t &unsure) {
+    const uint32_t addr = (uint32_t)__cvta_generic_to_shared(win);
+    const uint32_t *wp = reinterpret_cast<const uint32_t *>(win - (addr & 2u));
+    const uint32_t sh = (addr & 2u) * 8u;
+    uint32_t w[9];
+#pragma unroll
+    for (int k = 0; k < 9; k++) w[k] = wp[k];
+    float re[16], im[16];
+#pragma unroll
+    for (int k = 0; k < 8; k++) {
+        const uint32_t pr = __funnelshift_r(w[k], w[k + 1], sh);   // I, Q of samples 2k, 2k + 1
+        const float i0 = __uint_as_float(__byte_perm(pr, 0x4B000000u, 0x7440u)) - 8388735.0f;
+        const float q0 = __uint_as_float(__byte_perm(pr, 0x4B000000u, 0x7441u)) - 8388735.0f;
+        const float i1 = __uint_as_float(__byte_perm(pr, 0x4B000000u, 0x7442u)) - 8388735.0f;
+        const float q1 = __uint_as_float(__byte_perm(pr, 0x4B000000u, 0x7443u)) - 8388735.0f;
+        if ((k & 1) == 0) { re[2 * k] = i0; im[2 * k] = q0; re[2 * k + 1] = -q1; im[2 * k + 1] = i1; }
+        else { re[2 * k] = -i0; im[2 * k] = -q0; re[2 * k + 1] = q1; im[2 * k + 1] = -i1; }
+    }
+    const float c0 = (float)DAVIS_C0, c1 = (float)DAVIS_C1, c2 = (float)DAVIS_C2,
+                c3 = (float)DAVIS_C3, c4 = (float)DAVIS_C4;
+    float fr[GRP_LANE + 1], fi[GRP_LANE + 1];                  // F of samples n0 - 1 .. n0 + 6
+#pragma unroll
+    for (int k = 0; k < GRP_LANE + 1; k++) {
+        float a = fmaf(c4, re[k + 4], guard_residual(k & 3, 0));
+        a = fmaf(c0, re[k] + re[k + 8], a);
+        a = fmaf(c1, re[k + 1] + re[k + 7], a);
+        a = fmaf(c2, re[k + 2] + re[k + 6], a);
+        fr[k] = fmaf(c3, re[k + 3] + re[k + 5], a);
+        float b = fmaf(c4, im[k + 4], guard_residual(k & 3, 1));
+        b = fmaf(c0, im[k] + im[k + 8], b);
+        b = fmaf(c1, im[k + 1] + im[k + 7], b);
+        b = fmaf(c2, im[k + 2] + im[k + 6], b);
+        fi[k] = fmaf(c3, im[k + 3] + im[k + 5], b);
+    }
+    uint32_t bits = 0;
+    unsure = 0;
+#pragma unroll
+    for (int t = 0; t < GRP_LANE; t++) {
+        const float t1 = __fmul_rn(fr[t], fi[t + 1]);
+        const float num = __fmaf_rn(fi[t], fr[t + 1], -t1);
+        const float s1 = (fabsf(fr[t]) + fabsf(fi[t])) + (fabsf(fr[t + 1]) + fabsf(fi[t + 1]));
+        const float s2 = fabsf(fi[t] * fr[t + 1]) + fabsf(t1);
+        const float tau = fmaf(1e-4f, s1, fmaf(2.3841858e-7f, s2, 1e-6f));
+        bits |= (__float_as_uint(num) >> 31) << t;
+        unsure |= (fabsf(num) <= tau ? 1u : 0u) << t;
+    }
+    return bits;
+}
+
+
+// what a warp fetches one iteration ahead for a queued group
+struct GroupFetch {
+    uint4 chunk;        // this lane's 16 bytes of the group's sample span
+    uint32_t old_word;  // the streaming kernel's bitmap word (lanes 0, 4, .. 28)
+    int64_t done;       // blocks_done of the stream
+};
+__device__ __forceinline__ GroupFetch fetch_group(const View &vw, const SearchParams &sp,
+                                                  const uint32_t *planes, uint2 e, int lane) {
+    constexpr int SPAN = GROUP_SAMPLES + 10;
+    GroupFetch f;
+    f.chunk = span_chunk(vw, (int)e.x, (int)e.y * GROUP_SAMPLES - 10, SPAN, lane);
+    f.old_word = (lane & 3) == 0
+        ? __ldcg(planes + (size_t)e.x * sp.words_alloc + (size_t)e.y * GROUP_WORDS + (lane >> 2)) : 0u;
+    f.done = __ldg(vw.blocks_done + e.x);
+    return f;
+}
+
+__global__ void __launch_bounds__(EXACT_WARPS * 32, 4)
 k_exact(View vw, SearchParams sp, uint32_t *__restrict__ planes, const uint2 *__restrict__ glist,
         Fix *__restrict__ fixes, Counters *ctr) {
     constexpr int SPAN = GROUP_SAMPLES + 10;
@@ -305,33 +397,52 @@ k_exact(View vw, SearchParams sp, uint32_t *__restrict__ planes, const uint2 *__
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const unsigned int n = min(ctr->n_grp, sp.grp_cap);
     const unsigned int warps = gridDim.x * EXACT_WARPS;
-    // the next group's span is fetched into a register while this one is computed
-    unsigned int gi = blockIdx.x * EXACT_WARPS + warp;
-    uint2 e = gi < n ? glist[gi] : make_uint2(0u, 0u);
-    uint4 chunk = gi < n ? span_chunk(vw, (int)e.x, (int)e.y * GROUP_SAMPLES - 10, SPAN, lane)
-                         : make_uint4(0u, 0u, 0u, 0u);
-    for (; gi < n; gi += warps) {
+    const unsigned int first = blockIdx.x * EXACT_WARPS + warp;
+    // Nothing a group needs is waited for in the iteration that uses it: the warp's
+    // list entries are held 32 at a time (lane k = entry of iteration 32 b + k, the next
+    // 32 loaded a whole batch ahead), and the span, the old bitmap word and the stream's
+    // block counter of iteration i + 1 are requested at the top of iteration i.
+    auto load_batch = [&](unsigned int it0) {
+        const unsigned long long gi = (unsigned long long)first + (unsigned long long)(it0 + lane) * warps;
+        return gi < n ? __ldg(glist + gi) : make_uint2(0u, 0u);
+    };
+    if (first >= n) return;
+    uint2 batch = load_batch(0), batch_next = make_uint2(0u, 0u);
+    uint2 e = make_uint2(__shfl_sync(0xFFFFFFFFu, batch.x, 0), __shfl_sync(0xFFFFFFFFu, batch.y, 0));
+    GroupFetch cur = fetch_group(vw, sp, planes, e, lane);
+    for (unsigned int it = 0;; it++) {
+        const unsigned int nit = it + 1;
+        const bool more = (unsigned long long)first + (unsigned long long)nit * warps < n;
+        if ((it & 31u) == 0) batch_next = load_batch(it + 32);
+        const uint2 src_batch = (nit & 31u) ? batch : batch_next;
+        const uint2 e_next = make_uint2(__shfl_sync(0xFFFFFFFFu, src_batch.x, nit & 31u),
+                                        __shfl_sync(0xFFFFFFFFu, src_batch.y, nit & 31u));
+        if ((nit & 31u) == 0) batch = batch_next;
+        GroupFetch nxt = cur;
+        if (more) nxt = fetch_group(vw, sp, planes, e_next, lane);
+
         const int s = (int)e.x, grp = (int)e.y;
         const int v_begin = grp * GROUP_SAMPLES - 10;
         __syncwarp();                                          // previous span fully consumed
-        const SpanSrc src = span_store(vw, s, v_begin, chunk,
-                                       reinterpret_cast<uint8_t *>(span_mem[warp]), lane);
-        if (gi + warps < n) {
-            e = glist[gi + warps];
-            chunk = span_chunk(vw, (int)e.x, (int)e.y * GROUP_SAMPLES - 10, SPAN, lane);
-        }
+        reinterpret_cast<uint4 *>(span_mem[warp])[lane] = cur.chunk;
+        __syncwarp();
+        SpanSrc src;
+        src.base = reinterpret_cast<const uint8_t *>(span_mem[warp]);
+        src.v0 = (int)(((2LL * v_begin) & ~15LL) >> 1);
+        src.g0 = cur.done * (int64_t)vw.block - vw.n_carry;
         const int n0 = grp * GROUP_SAMPLES + GRP_LANE * lane;  // first sample this lane decides
         uint32_t bits = 0;
         if (v_begin < 0 || src.g0 + v_begin < 0) {             // zero history in reach: generic path
 #pragma unroll 1
             for (int t = 0; t < GRP_LANE; t++) bits |= exact_bit(lut, src, n0 + t) << t;
         } else {
-            Cplx F[GRP_LANE + 1];                              // F of V samples n0 - 1 .. n0 + 6
-            fixed_filtered_run<GRP_LANE + 1>(lut, src, n0 - 1, F);
-#pragma unroll
-            for (int t = 0; t < GRP_LANE; t++)
-                bits |= (uint32_t)((unsigned long long)__double_as_longlong(exact_cross(F[t], F[t + 1])) >> 63)
-                        << t;
+            uint32_t unsure;
+            bits = guarded_bits(src.base + 2 * (n0 - 10 - src.v0), unsure);
+            while (unsure) {                                   // rare: |numerator| inside the guard band
+                const int t = __ffs(unsure) - 1;
+                unsure &= unsure - 1;
+                bits = (bits & ~(1u << t)) | (exact_bit(lut, src, n0 + t) << t);
+            }
         }
         // four lanes make one 28-bit word
         uint32_t word = bits << (GRP_LANE * (lane & 3));
@@ -339,15 +450,19 @@ k_exact(View vw, SearchParams sp, uint32_t *__restrict__ planes, const uint2 *__
         word |= __shfl_xor_sync(0xFFFFFFFFu, word, 2);
         if ((lane & 3) == 0) {
             const int wi = grp * GROUP_WORDS + (lane >> 2);
-            uint32_t *p = planes + (size_t)s * sp.words_alloc + wi;
-            const uint32_t diff = (*p ^ word) & MASK28;
-            *p = word;
+            const uint32_t diff = (cur.old_word ^ word) & MASK28;
             // words past the end of the call's samples hold no decisions anyone reads
-            if (diff && (long long)LANE_SAMPLES * (wi + 1) <= (long long)vw.n_carry + vw.n_new) {
-                const unsigned int at = atomicAdd(&ctr->n_fix, 1u);
-                if (at < FIX_CAP) fixes[at] = Fix{(uint32_t)s, (uint32_t)wi, diff, 0u};
+            if (diff) {
+                planes[(size_t)s * sp.words_alloc + wi] = word;
+                if ((long long)LANE_SAMPLES * (wi + 1) <= (long long)vw.n_carry + vw.n_new) {
+                    const unsigned int at = atomicAdd(&ctr->n_fix, 1u);
+                    if (at < FIX_CAP) fixes[at] = Fix{(uint32_t)s, (uint32_t)wi, diff, 0u};
+                }
             }
         }
+        if (!more) break;
+        e = e_next;
+        cur = nxt;
     }
 }
 

@@ -83,7 +83,7 @@ def test_fan_in_files_equal_direct_submit_and_parse(tmp_path):
     paths = []
     for n, c in zip(names, caps):
         p = tmp_path / (n + ".u8")
-        c.tofile(p)
+        c[: n_blocks * 16384].tofile(p)     # equal lengths: no stream is fed idle blocks
         paths.append(str(p))
     cfg = protocol.new_packet_config(14)
     with dsp.BatchDemodulator(cfg, 2, max_blocks=n_blocks) as direct:
@@ -103,4 +103,12 @@ def test_fan_in_files_equal_direct_submit_and_parse(tmp_path):
         assert p["data"] == bytes(protocol.swap_bit_order(x) for x in h["data"])[2:]
         assert p["id"] == p["data"][0] & 7
         assert p["freq_err"] == -int(float(h["disc_mean"]) * 268800 / (2 * math.pi))
+    # the discriminator mean is the reference's mean(discriminated[index:index+224]),
+    # i.e. D over the 224 samples from the preamble's global position (protocol.py:304-310)
+    from oracle import davis_oracle as O
+    disc = [O.stream_discriminated(c[: n_blocks * 16384]) for c in caps]
+    for h in valid:
+        g = int(h["position"])
+        np.testing.assert_allclose(float(h["disc_mean"]), disc[int(h["stream"])][g:g + 224].mean(),
+                                   rtol=1e-9, atol=1e-13)
     assert protocol.parse_hits(want, cfg, station_id=5) == [p for p in parsed if p["id"] == 5]
