@@ -121,10 +121,11 @@ k_search(const uint32_t *__restrict__ words, SearchParams sp, unsigned int s_off
         const int w0 = (int)((unsigned int)id - sl * (unsigned int)quads) * SEARCH_WORDS;
         const unsigned int s = s_off + sl;
 
-        // First stage, word-parallel.  At most one differing symbol means the first
-        // eight or the last eight symbols match exactly: two AND chains (one LOP3 per
-        // symbol) find those positions for all 28 phases of a word at once (2 * 2^-8
-        // of the positions of noise).
+        // First stage, word-parallel.  At most one differing symbol means at least three
+        // of the four quarters of the sync word match exactly: four AND chains (one LOP3
+        // per symbol) and a 3-of-4 vote find those positions for all 28 phases of a word
+        // at once (4 * 2^-12 of the positions of noise; the previous first-half-or-last-
+        // half test let 2 * 2^-8 through, and queueing those was 40 % of the kernel).
         uint32_t hit[SEARCH_WORDS];
 #pragma unroll
         for (int k = 0; k < SEARCH_WORDS; k++) hit[k] = 0;
@@ -140,15 +141,16 @@ k_search(const uint32_t *__restrict__ words, SearchParams sp, unsigned int s_off
             for (int m = 0; m < SEARCH_WORDS + 7; m++) h[m] = (e[m] >> SPS) | (e[m + 1] << SPS);
 #pragma unroll
             for (int k = 0; k < SEARCH_WORDS; k++) {
-                uint32_t first = MASK28, last = MASK28;
+                // quarters of the sync word (4 symbols each) that match exactly
+                uint32_t qt[4];
 #pragma unroll
-                for (int m = 0; m < 4; m++) {
-                    first &= e[k + m] ^ inv[2 * m];
-                    first &= h[k + m] ^ inv[2 * m + 1];
-                    last &= e[k + 4 + m] ^ inv[8 + 2 * m];
-                    last &= h[k + 4 + m] ^ inv[8 + 2 * m + 1];
+                for (int j = 0; j < 4; j++) {
+                    qt[j] = (e[k + 2 * j] ^ inv[4 * j]) & (h[k + 2 * j] ^ inv[4 * j + 1]);
+                    qt[j] &= e[k + 2 * j + 1] ^ inv[4 * j + 2];
+                    qt[j] &= h[k + 2 * j + 1] ^ inv[4 * j + 3];
                 }
-                hit[k] = first | last;
+                // at most one differing symbol => at least three quarters match
+                hit[k] = ((qt[0] & qt[1] & (qt[2] | qt[3])) | (qt[2] & qt[3] & (qt[0] | qt[1]))) & MASK28;
             }
         }
 
