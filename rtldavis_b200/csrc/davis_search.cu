@@ -28,7 +28,7 @@ namespace davis {
 constexpr int SEARCH_THREADS = 256;
 constexpr uint32_t MASK28 = 0x0FFFFFFFu;
 
-constexpr int SEARCH_WORDS = 4;      // bitmap words per thread (one 16-byte load + 8 words of lookahead)
+constexpr int SEARCH_WORDS = 8;      // bitmap words per thread (two 16-byte loads + 8 words of lookahead)
 constexpr int SEARCH_WARPS = SEARCH_THREADS / 32;
 constexpr int QUEUE = 160;           // per-warp queue of positions that passed the prefilter
 
@@ -157,7 +157,9 @@ k_search(const uint32_t *__restrict__ words, SearchParams sp, unsigned int s_off
         // Compact the surviving positions of the whole warp into its queue (one
         // exclusive scan of the per-lane counts, then every lane writes its own);
         // the queue is checked densely (every lane one position) when it fills up.
-        const int mine = __popc(hit[0]) + __popc(hit[1]) + __popc(hit[2]) + __popc(hit[3]);
+        int mine = 0;
+#pragma unroll
+        for (int k = 0; k < SEARCH_WORDS; k++) mine += __popc(hit[k]);
         int incl = mine;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
