@@ -41,7 +41,7 @@ BLOCK = 8192
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="graft", choices=["graft", "reference"])
     ap.add_argument("--streams", type=int, default=1024, help="streams per GPU")
@@ -148,18 +148,21 @@ class ClockSampler:
 
     def _poll(self):
         nv = self.nv
+        i, pw = 0, 0.0
         while not self.stop_flag.is_set():
             try:
                 sm = nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)
-                pw = nv.nvmlDeviceGetPowerUsage(self.h) / 1000.0
                 try:
                     rs = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
                 except Exception:
                     rs = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                if i % 8 == 0:                      # the power query is the slow one
+                    pw = nv.nvmlDeviceGetPowerUsage(self.h) / 1000.0
                 self.rows.append((float(sm), pw, int(rs)))
             except Exception:
                 pass
-            time.sleep(0.0005)
+            i += 1
+            time.sleep(0.0002)
 
     def start(self):
         if self.h is None:
