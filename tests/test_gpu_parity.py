@@ -462,3 +462,43 @@ def test_input_type_change_needs_reset(dsp):
     with pytest.raises(ValueError):
         dem.demodulate(np.zeros(B - 1, dtype=np.complex64))
     dem.close()
+
+
+# ---------------------------------------------------------------------------
+# what the reference attaches to a Packet, at scale (byte input)
+# ---------------------------------------------------------------------------
+def test_rssi_snr_and_disc_mean_match_call_oracle(dsp, protocol):
+    """RSSI/SNR (dsp.py:207-236, with the reference's misaligned windows) and the
+    discriminator mean Parser.parse takes (protocol.py:304-310) for every packet of a
+    seeded batch, against the call-by-call oracle: first calls of a fresh stream (zero
+    history), index near 0 and near block_size (clipped windows), low SNR."""
+    from rtldavis_b200 import synth
+    n_streams, n_blocks, B = 8, 14, 8192
+    iq, truth = synth.make_batch(n_streams, n_blocks * B, 12, 14.0, seed0=900, df_range_hz=2500.0,
+                                 ppm_range=30.0)
+    # a burst right at the start of stream 0 so that its windows reach the zero history:
+    # the sync word (after 32 training symbols) lands ~150 samples into the stream
+    t0 = truth[1][2].start + 300
+    iq[0, : 2 * 2000] = iq[1, 2 * t0: 2 * (t0 + 2000)]
+    want = {}
+    for s in range(n_streams):
+        orc = O.CallOracle(O.OracleConfig())
+        for k in range(n_blocks):
+            for p in orc.demodulate(iq[s, 2 * B * k: 2 * B * (k + 1)]):
+                dm = float(np.mean(orc.discriminated[p.index:p.index + 224]))
+                want[(s, k, p.index, p.data)] = (p.rssi, p.snr, dm)
+    assert len(want) > 40
+    bd = dsp.BatchDemodulator(protocol.new_packet_config(14), n_streams, max_blocks=n_blocks)
+    bd.submit(iq)
+    hits = bd.fetch()
+    got = {(int(h["stream"]), int(h["call"]), int(h["index"]), h["data"].tobytes()):
+           (float(h["rssi"]), float(h["snr"]), float(h["disc_mean"])) for h in hits}
+    assert set(got) == set(want)
+    keys = sorted(want)
+    w = np.array([want[k] for k in keys])
+    g = np.array([got[k] for k in keys])
+    np.testing.assert_allclose(g[:, 0], w[:, 0], rtol=0, atol=1e-9)      # dB
+    np.testing.assert_allclose(g[:, 1], w[:, 1], rtol=0, atol=1e-9)      # dB
+    np.testing.assert_allclose(g[:, 2], w[:, 2], rtol=1e-9, atol=1e-13)
+    assert any(k[1] <= 1 for k in keys)          # a packet of the first calls is among them
+    bd.close()
