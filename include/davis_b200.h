@@ -76,7 +76,8 @@ typedef struct davis_hit {
     uint8_t flags;        /* bit0: a decision bit was corrected by the fp64 re-check */
     double rssi;          /* Packet.rssi, dsp.py:207-229                            */
     double snr;           /* Packet.snr,  dsp.py:230-236                            */
-    double disc_mean;     /* mean(discriminated[index:index+224]), protocol.py:304-310 */
+    double disc_mean;     /* mean(discriminated[index:index+224]), protocol.py:304-310;
+                             NaN when crc_ok == 0 (the reference takes it after the CRC gate) */
 } davis_hit;
 
 typedef struct davis_handle davis_handle;

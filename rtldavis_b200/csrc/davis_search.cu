@@ -786,7 +786,8 @@ k_finalize(View vw, SearchParams sp, const Rec *__restrict__ recs,
         const double sig = power_sum(lut, sp_p, f0 + q, f0 + s1, lane) / (double)(s1 - q);
         const double noise = q > n0 ? power_sum(lut, sp_p, f0 + n0, f0 + q, lane) / (double)(q - n0)
                                     : 1e-9;
-        const double dsum = disc_sum(lut, sp_d, d0, lane);
+        // protocol.py:297-310: only a packet that passes the CRC gate has its mean taken
+        const double dsum = r.crc_ok ? disc_sum(lut, sp_d, d0, lane) : 0.0;
         if (lane == 0) {
             const unsigned int at = atomicAdd(&ctr->n_hit, 1u);   // <= n_rec <= hit_cap
             atomicAdd(&per_stream[s], 1u);
@@ -801,7 +802,7 @@ k_finalize(View vw, SearchParams sp, const Rec *__restrict__ recs,
             h.flags = r.flags;
             h.rssi = sig > 0.0 ? 10.0 * log10(sig) : -120.0;
             h.snr = noise > 0.0 ? 10.0 * log10(sig / noise) : 50.0;
-            h.disc_mean = dsum / (double)PRE;
+            h.disc_mean = r.crc_ok ? dsum / (double)PRE : __longlong_as_double(0x7FF8000000000000LL);
             hits[at] = h;
         }
     }
@@ -1003,18 +1004,21 @@ k_finalize_u8(View vw, SearchParams sp, const Rec *__restrict__ recs,
             const uint8_t *bp = reinterpret_cast<const uint8_t *>(mem_p[warp]);
             const uint8_t *bd = reinterpret_cast<const uint8_t *>(mem_d[warp]);
             const int q = g.q;
-            double sig, noise, dsum;
+            // Parser.parse takes the discriminator mean only after the CRC gate
+            // (protocol.py:297-310): it is not computed for a packet that fails it
+            const bool want_disc = ((__shfl_sync(0xFFFFFFFFu, rw[8], k) >> 16) & 0xFFu) != 0;
+            double sig, noise, dsum = 0.0;
             if (pv < 0 || dv < 0 || g0 + pv < 0 || g0 + dv < 0) {          // zero history in reach
                 SpanSrc sp_p, sp_d;
                 sp_p.base = bp; sp_p.v0 = pvb; sp_p.g0 = g0;
                 sp_d.base = bd; sp_d.v0 = dvb; sp_d.g0 = g0;
                 sig = power_sum(lut, sp_p, g.f0 + q, g.f0 + g.s1, lane);
                 noise = q > g.n0 ? power_sum(lut, sp_p, g.f0 + g.n0, g.f0 + q, lane) : 0.0;
-                dsum = disc_sum(lut, sp_d, g.d0, lane);
+                if (want_disc) dsum = disc_sum(lut, sp_d, g.d0, lane);
             } else {
                 sig = int_power_sum(bp, pvb, g.f0 + q, g.f0 + g.s1, lane) * (1.0 / LUT_SCALE2);
                 noise = q > g.n0 ? int_power_sum(bp, pvb, g.f0 + g.n0, g.f0 + q, lane) * (1.0 / LUT_SCALE2) : 0.0;
-                dsum = int_disc_sum(bd, dvb, g.d0, lane);
+                if (want_disc) dsum = int_disc_sum(bd, dvb, g.d0, lane);
             }
             sig /= (double)(g.s1 - q);
             noise = q > g.n0 ? noise / (double)(q - g.n0) : 1e-9;
@@ -1037,7 +1041,7 @@ k_finalize_u8(View vw, SearchParams sp, const Rec *__restrict__ recs,
                 h.flags = (uint8_t)(f[8] >> 24);
                 h.rssi = sig > 0.0 ? 10.0 * log10(sig) : -120.0;
                 h.snr = noise > 0.0 ? 10.0 * log10(sig / noise) : 50.0;
-                h.disc_mean = dsum / (double)PRE;
+                h.disc_mean = want_disc ? dsum / (double)PRE : __longlong_as_double(0x7FF8000000000000LL);
                 hits[at] = h;
             }
             if (kn < 0) break;

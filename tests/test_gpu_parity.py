@@ -492,13 +492,16 @@ def test_rssi_snr_and_disc_mean_match_call_oracle(dsp, protocol):
     bd.submit(iq)
     hits = bd.fetch()
     got = {(int(h["stream"]), int(h["call"]), int(h["index"]), h["data"].tobytes()):
-           (float(h["rssi"]), float(h["snr"]), float(h["disc_mean"])) for h in hits}
+           (float(h["rssi"]), float(h["snr"]), float(h["disc_mean"]), bool(h["crc_ok"])) for h in hits}
     assert set(got) == set(want)
     keys = sorted(want)
     w = np.array([want[k] for k in keys])
-    g = np.array([got[k] for k in keys])
+    g = np.array([got[k][:3] for k in keys])
+    ok = np.array([got[k][3] for k in keys])
     np.testing.assert_allclose(g[:, 0], w[:, 0], rtol=0, atol=1e-9)      # dB
     np.testing.assert_allclose(g[:, 1], w[:, 1], rtol=0, atol=1e-9)      # dB
-    np.testing.assert_allclose(g[:, 2], w[:, 2], rtol=1e-9, atol=1e-13)
+    # the mean is taken after the CRC gate (protocol.py:297-310): NaN for the others
+    assert ok.sum() >= 20 and np.isnan(g[~ok, 2]).all()
+    np.testing.assert_allclose(g[ok, 2], w[ok, 2], rtol=1e-9, atol=1e-13)
     assert any(k[1] <= 1 for k in keys)          # a packet of the first calls is among them
     bd.close()
