@@ -800,8 +800,8 @@ k_finalize(View vw, SearchParams sp, const Rec *__restrict__ recs,
             for (int b = 0; b < PKT_BYTES; b++) h.data[b] = r.data[b];
             h.crc_ok = r.crc_ok;
             h.flags = r.flags;
-            h.rssi = sig > 0.0 ? 10.0 * log10(sig) : -120.0;
-            h.snr = noise > 0.0 ? 10.0 * log10(sig / noise) : 50.0;
+            h.rssi = sig;                                     // mean powers; k_order takes the
+            h.snr = noise;                                    // logarithms, one thread per packet
             h.disc_mean = r.crc_ok ? dsum / (double)PRE : __longlong_as_double(0x7FF8000000000000LL);
             hits[at] = h;
         }
@@ -1039,8 +1039,8 @@ k_finalize_u8(View vw, SearchParams sp, const Rec *__restrict__ recs,
                 for (int bb = 0; bb < PKT_BYTES; bb++) h.data[bb] = (uint8_t)(dw[bb >> 2] >> (8 * (bb & 3)));
                 h.crc_ok = (uint8_t)(f[8] >> 16);
                 h.flags = (uint8_t)(f[8] >> 24);
-                h.rssi = sig > 0.0 ? 10.0 * log10(sig) : -120.0;
-                h.snr = noise > 0.0 ? 10.0 * log10(sig / noise) : 50.0;
+                h.rssi = sig;                                 // mean powers; k_order takes the
+                h.snr = noise;                                // logarithms, one thread per packet
                 h.disc_mean = want_disc ? dsum / (double)PRE : __longlong_as_double(0x7FF8000000000000LL);
                 hits[at] = h;
             }
@@ -1154,7 +1154,14 @@ k_order(const davis_hit *__restrict__ hits, const unsigned int *__restrict__ sta
             if (e < n)
                 for (unsigned int j = 0; j < tn; j++) rank += keys[j] < mine;
         }
-        if (e < n) out[base + rank] = hits[src];
+        if (e < n) {
+            davis_hit h = hits[src];
+            // dsp.py:226-236 on the mean powers the finalize kernel left in rssi / snr
+            const double sig = h.rssi, noise = h.snr;
+            h.rssi = sig > 0.0 ? 10.0 * log10(sig) : -120.0;
+            h.snr = noise > 0.0 ? 10.0 * log10(sig / noise) : 50.0;
+            out[base + rank] = h;
+        }
     }
 }
 
