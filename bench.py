@@ -382,7 +382,7 @@ def run_graft(a):
             "config": {"workload": workload_name(a), "streams_per_gpu": a.streams,
                        "blocks_per_stream": a.blocks, "block_size": BLOCK,
                        "l2": "inputs (%.2f GB per GPU) far exceed the 126 MB L2" % (a.streams * row / 1e9),
-                       "decision_arithmetic": "fp32 streaming kernel, every reported packet re-derived in fp64"},
+                       "decision_arithmetic": "fp32 streaming kernel; every bit of every reported packet re-derived with an error bound (fp32 outside the guard band, fp64 inside), RSSI/SNR/discriminator mean in fp64"},
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e,
             "gpu_launches": int(launches), "clocks": clocks,
             "valid_packets_per_step": int(n_valid.item()),
