@@ -261,14 +261,21 @@ k_precheck(View vw, SearchParams sp, const Cand *__restrict__ cand, Cand *__rest
         unsigned int fresh[8];
         int n_fresh = 0;
         if (pass && !bitmap_is_exact) {
+            // the position's groups g0..g1 (at most 7) lie in one or two mark words: read
+            // both, then one atomicOr per word with every missing bit at once (a load and
+            // an atomic per group made this loop a chain of up to 12 L2 round trips)
             const int g0 = c.v / GROUP_SAMPLES, g1 = (c.v + SPS * (PKT_SYMS - 1)) / GROUP_SAMPLES;
             uint32_t *row = marks + (size_t)c.stream * sp.mark_words;
-            for (int g = g0; g <= g1; g++) {
-                const uint32_t bit = 1u << (g & 31);
-                if (row[g >> 5] & bit) continue;                // cheap pre-test; atomicOr decides
-                if (atomicOr(&row[g >> 5], bit) & bit) continue;
-                fresh[n_fresh++] = (unsigned int)g;
-            }
+            const int w0 = g0 >> 5, w1 = g1 >> 5;
+            const uint32_t span = g1 - g0 + 1;                       // <= 7 bits
+            const unsigned long long bits = ((1ull << span) - 1ull) << (g0 & 31);
+            const uint32_t m0 = (uint32_t)bits, m1 = (uint32_t)(bits >> 32);
+            const uint32_t p0 = row[w0], p1 = w1 != w0 ? row[w1] : 0xFFFFFFFFu;
+            uint32_t f0 = m0 & ~p0, f1 = m1 & ~p1;
+            if (f0) f0 &= ~atomicOr(&row[w0], f0);
+            if (f1) f1 &= ~atomicOr(&row[w1], f1);
+            while (f0) { fresh[n_fresh++] = (unsigned int)(32 * w0 + __ffs(f0) - 1); f0 &= f0 - 1; }
+            while (f1) { fresh[n_fresh++] = (unsigned int)(32 * w1 + __ffs(f1) - 1); f1 &= f1 - 1; }
         }
         const uint32_t pm = __ballot_sync(0xFFFFFFFFu, pass);
         unsigned int incl = (unsigned int)n_fresh;
