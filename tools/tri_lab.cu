@@ -17,17 +17,43 @@ __device__ __forceinline__ float2 f2(float a, float b) { return make_float2(a, b
 __device__ __forceinline__ float2 cadd(float2 a, float2 b) { return __fadd2_rn(a, b); }
 __device__ __forceinline__ float2 cfma(float2 a, float2 b, float2 c) { return __ffma2_rn(a, b, c); }
 
+#ifndef CONV
+#define CONV 0      // 0: every byte PRMT + centring add; 1: even window indices by I2F.S8 of (u ^ 0x80)
+#endif
 __host__ __device__ constexpr double residual(int q, int comp) {
     const double c[9] = {C0, C1, C2, C3, C4, C3, C2, C1, C0};
+#if CONV == 1
+    // even indices are centred at 128 (u - 127.4 = (u - 128) + 0.6), odd ones at 127
+    const double sre[4] = {0.6, 0.4, -0.6, -0.4}, sim[4] = {0.6, -0.4, -0.6, 0.4};
+#else
     const double sre[4] = {-0.4, 0.4, 0.4, -0.4}, sim[4] = {-0.4, -0.4, 0.4, 0.4};
+#endif
     double acc = 0.0;
     for (int m = 0; m < 9; m++) acc += c[m] * (comp ? sim[(q + 2 + m) & 3] : sre[(q + 2 + m) & 3]);
     return acc;
 }
 
 // ---- packed fp32 pair of runs ---------------------------------------------------
+// byte B of x as a signed 8-bit integer -> float: compiles to one I2F.S8 with a byte selector
+template <int B>
+__device__ __forceinline__ float s8f(uint32_t x) {
+    float a;
+    asm("{ .reg .b32 t; .reg .b16 h; bfe.s32 t, %1, %2, 8; cvt.s8.s32 h, t; cvt.rn.f32.s16 %0, h; }"
+        : "=f"(a) : "r"(x), "n"(8 * B));
+    return a;
+}
 template <int I>
 __device__ __forceinline__ void conv_pair(uint32_t wa, uint32_t wb, float2 &re, float2 &im) {
+#if CONV == 1
+    if ((I & 1) == 0) {          // bytes 0, 1 of the word; XU pipe, no PRMT, no centring add
+        const uint32_t xa = wa ^ 0x80808080u, xb = wb ^ 0x80808080u;
+        const float2 vi = f2(s8f<0>(xa), s8f<0>(xb));
+        const float2 vq = f2(s8f<1>(xa), s8f<1>(xb));
+        if ((I & 3) == 0) { re = vi; im = vq; }
+        else { re = f2(-vi.x, -vi.y); im = f2(-vq.x, -vq.y); }
+        return;
+    }
+#endif
     constexpr uint32_t selI = (I & 1) ? 0x7442u : 0x7440u, selQ = (I & 1) ? 0x7443u : 0x7441u;
     const float2 mI = f2(__uint_as_float(__byte_perm(wa, 0x4B000000u, selI)),
                          __uint_as_float(__byte_perm(wb, 0x4B000000u, selI)));
