@@ -96,6 +96,32 @@ __device__ __forceinline__ void search_drain(const uint32_t *__restrict__ words,
     }
 }
 
+// One quarter of the sync word (symbols 4J .. 4J+3) for all 28 phases of a word: bit b set
+// iff the four symbols of the position at bit b match.  PAT = the sync word with symbol 0 in
+// bit 0, known at compile time: the polarity of three symbols goes into one LOP3 truth
+// table (2 LOP3 per quarter).  PAT = 0: polarity from the run-time masks inv[] (4 LOP3).
+template <uint32_t PAT, int J>
+__device__ __forceinline__ uint32_t quarter_match(uint32_t x0, uint32_t x1, uint32_t x2, uint32_t x3,
+                                                  const uint32_t (&inv)[PRE_SYMS]) {
+    if constexpr (PAT == 0) {
+        uint32_t q = (x0 ^ inv[4 * J]) & (x1 ^ inv[4 * J + 1]);
+        q &= x2 ^ inv[4 * J + 2];
+        q &= x3 ^ inv[4 * J + 3];
+        return q;
+    } else {
+        constexpr uint32_t p0 = (PAT >> (4 * J)) & 1u, p1 = (PAT >> (4 * J + 1)) & 1u,
+                           p2 = (PAT >> (4 * J + 2)) & 1u, p3 = (PAT >> (4 * J + 3)) & 1u;
+        // table index = a*4 + b*2 + c; the only set entry is (a, b, c) = (p0, p1, p2)
+        constexpr uint32_t lut3 = 1u << (p0 * 4 + p1 * 2 + p2);
+        uint32_t first, q;
+        asm("lop3.b32 %0, %1, %2, %3, %4;" : "=r"(first) : "r"(x0), "r"(x1), "r"(x2), "n"(lut3));
+        // first & x3 (0xC0) or first & ~x3 (0x30); the third operand is unused
+        asm("lop3.b32 %0, %1, %2, %2, %3;" : "=r"(q) : "r"(first), "r"(x3), "n"(p3 ? 0xC0 : 0x30));
+        return q;
+    }
+}
+
+template <uint32_t PAT>
 __global__ void __launch_bounds__(SEARCH_THREADS)
 k_search(const uint32_t *__restrict__ words, SearchParams sp, unsigned int s_off,
          Cand *__restrict__ cand, Counters *ctr) {
@@ -143,12 +169,10 @@ k_search(const uint32_t *__restrict__ words, SearchParams sp, unsigned int s_off
             for (int k = 0; k < SEARCH_WORDS; k++) {
                 // quarters of the sync word (4 symbols each) that match exactly
                 uint32_t qt[4];
-#pragma unroll
-                for (int j = 0; j < 4; j++) {
-                    qt[j] = (e[k + 2 * j] ^ inv[4 * j]) & (h[k + 2 * j] ^ inv[4 * j + 1]);
-                    qt[j] &= e[k + 2 * j + 1] ^ inv[4 * j + 2];
-                    qt[j] &= h[k + 2 * j + 1] ^ inv[4 * j + 3];
-                }
+                qt[0] = quarter_match<PAT, 0>(e[k], h[k], e[k + 1], h[k + 1], inv);
+                qt[1] = quarter_match<PAT, 1>(e[k + 2], h[k + 2], e[k + 3], h[k + 3], inv);
+                qt[2] = quarter_match<PAT, 2>(e[k + 4], h[k + 4], e[k + 5], h[k + 5], inv);
+                qt[3] = quarter_match<PAT, 3>(e[k + 6], h[k + 6], e[k + 7], h[k + 7], inv);
                 // at most one differing symbol => at least three quarters match
                 hit[k] = ((qt[0] & qt[1] & (qt[2] | qt[3])) | (qt[2] & qt[3] & (qt[0] | qt[1]))) & MASK28;
             }
@@ -221,7 +245,11 @@ void launch_search(const uint32_t *words, const SearchParams &sp, Cand *cand, Co
         part.n_streams = (int)std::min<long long>(per_launch, sp.n_streams - s0);
         const long long total = part.n_streams * quads;
         const unsigned grid = (unsigned)std::min<long long>((total + SEARCH_THREADS - 1) / SEARCH_THREADS, 148LL * 8);
-        k_search<<<grid, SEARCH_THREADS, 0, st>>>(words, part, (unsigned int)s0, cand, ctr);
+        // the Davis sync word 0xCB89 (symbol 0 in bit 0: 0x91D3) has its polarity compiled in
+        if (sp.pat_rev == 0x91D3u)
+            k_search<0x91D3u><<<grid, SEARCH_THREADS, 0, st>>>(words, part, (unsigned int)s0, cand, ctr);
+        else
+            k_search<0u><<<grid, SEARCH_THREADS, 0, st>>>(words, part, (unsigned int)s0, cand, ctr);
     }
 }
 

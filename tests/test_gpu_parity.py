@@ -505,3 +505,20 @@ def test_rssi_snr_and_disc_mean_match_call_oracle(dsp, protocol):
     np.testing.assert_allclose(g[ok, 2], w[ok, 2], rtol=1e-9, atol=1e-13)
     assert any(k[1] <= 1 for k in keys)          # a packet of the first calls is among them
     bd.close()
+
+
+def test_other_sync_word_uses_the_generic_search(dsp):
+    """The search kernel has the Davis sync word's polarity compiled in; any other
+    PacketConfig.preamble takes the run-time path.  0xAACB (the last training byte and
+    the first sync byte) occurs in every burst, 8 symbols before the sync word."""
+    iq, _ = _batch(6, 10, 20.0, seed0=700, df_range_hz=2000.0)
+    cfg = dsp.PacketConfig(19200, 14, 16, 80, "1010101011001011", block_size=8192)
+    bd = dsp.BatchDemodulator(cfg, 6, max_blocks=10)
+    bd.submit(iq)
+    hits = bd.fetch()
+    rec = CO.batch_records(iq, preamble=0xAACB)
+    want = [(int(r["stream"]), int(r["call"]), int(r["index"]), r["data"].tobytes(), bool(r["crc_ok"]))
+            for r in rec]
+    assert len(want) >= 6 and _gpu_rows(hits) == want
+    assert all(h["data"][0] == 0xAA and h["data"][1] == 0xCB for h in hits)
+    bd.close()
