@@ -211,7 +211,7 @@ def run_reference(a):
     iq, _ = synth.make_batch(n_distinct, sample_blocks * BLOCK,
                              max(1, a.packets * sample_blocks // 328), a.snr, seed0=a.seed,
                              df_range_hz=3000.0, ppm_range=50.0)
-    per_step = max(1.0, min(a.cpu_seconds, 240.0 / max(1, a.steps + a.warmup)))
+    per_step = max(1.0, min(a.cpu_seconds, 150.0 / max(1, a.steps + a.warmup)))  # whole run <= ~2.5 min
     rates = []
     for i in range(a.warmup + a.steps):
         rate, samples, wall = cpu_reference_rate(iq, per_step, cores, literal=True)
