@@ -522,3 +522,75 @@ def test_other_sync_word_uses_the_generic_search(dsp):
     assert len(want) >= 6 and _gpu_rows(hits) == want
     assert all(h["data"][0] == 0xAA and h["data"][1] == 0xCB for h in hits)
     bd.close()
+
+
+# ---------------------------------------------------------------------------
+# BASELINE configs[1] at full size: size-independent properties
+# ---------------------------------------------------------------------------
+def test_full_size_batch_properties(dsp, protocol):
+    """1 024 streams x 328 blocks (10 s each), generated on the device (the oracle would
+    need minutes).  Properties: (a) encode -> channel -> decode round trip: >= 99.5 % of
+    the embedded packets come back CRC-valid from their own stream (the rest start in the
+    never-flushed last block or overlap the capture edge); (b) any chunking of the streams
+    gives the same records (carried state): one call of 328 blocks == calls of 100 + 228;
+    (c) records arrive ordered by (stream, call, index mod 14, index) with no payload
+    twice in a (stream, call); (d) CRC verdicts agree with a host-side CRC of the bytes."""
+    import torch
+    from rtldavis_b200 import _lib
+    L = _lib.load()
+    n_streams, n_blocks, n_packets = 1024, 328, 40
+    n_samples = n_blocks * 8192
+    free, _ = torch.cuda.mem_get_info()
+    if free < 12 * 2 ** 30:
+        pytest.skip("needs 12 GB of free device memory")
+    buf = torch.empty((n_streams, 2 * n_samples), dtype=torch.uint8, device="cuda")
+    _lib.check(L.davis_synth_fill(buf.data_ptr(), n_streams, 2 * n_samples, n_samples, 777,
+                                  n_packets, 20.0, 3000.0, 50.0, 0, None))
+    torch.cuda.synchronize()
+    msgs = np.zeros((n_streams, n_packets, 8), dtype=np.uint8)
+    starts = np.zeros((n_streams, n_packets), dtype=np.int64)
+    _lib.check(L.davis_synth_truth(n_streams, n_samples, 777, n_packets, 20.0,
+                                   msgs.ctypes.data, starts.ctypes.data))
+    cfg = protocol.new_packet_config(14)
+    with dsp.BatchDemodulator(cfg, n_streams, max_blocks=n_blocks) as bd:
+        bd.submit(buf)
+        whole = bd.fetch()
+    with dsp.BatchDemodulator(cfg, n_streams, max_blocks=228) as bd:
+        bd.submit(buf[:, : 100 * 16384])
+        a = bd.fetch()
+        bd.submit(buf[:, 100 * 16384:])
+        b = bd.fetch()
+    del buf
+    # (b) chunking
+    split = np.concatenate([a, b])
+    cols = ["stream", "call", "index", "crc_ok", "position"]
+    key = lambda h: np.concatenate([np.stack([h[c].astype(np.int64) for c in cols], 1),
+                                    h["data"].astype(np.int64)], 1)
+    kw, ks = key(whole), key(split)
+    assert kw.shape == ks.shape
+    assert np.array_equal(kw[np.lexsort(kw.T[::-1])], ks[np.lexsort(ks.T[::-1])])
+    np.testing.assert_allclose(np.sort(whole["rssi"]), np.sort(split["rssi"]), rtol=0, atol=1e-9)
+    # (c) order and per-call dedupe
+    o = np.stack([whole["stream"].astype(np.int64), whole["call"].astype(np.int64),
+                  whole["index"].astype(np.int64) % 14, whole["index"].astype(np.int64)], 1)
+    d = np.diff(o, axis=0)
+    first_nz = np.argmax(d != 0, axis=1)
+    assert np.all(d[np.arange(d.shape[0]), first_nz] > 0), "records out of the reference's order"
+    per_call = np.concatenate([o[:, :2], whole["data"].astype(np.int64)], 1)
+    assert np.unique(per_call, axis=0).shape[0] == per_call.shape[0], "payload twice in one call"
+    # (d) CRC verdicts (crc.py:19-42 on the bit-swapped bytes 2..9)
+    pick = np.random.default_rng(1).choice(whole.shape[0], 4000, replace=False)
+    for i in pick:
+        h = whole[i]
+        sw = bytes(O.swap_bit_order(int(x)) for x in h["data"])
+        assert (O.crc16(sw[2:]) == 0) == bool(h["crc_ok"])
+    # (a) round trip
+    valid = whole[whole["crc_ok"] != 0]
+    got = {(int(s), bytes(protocol.swap_bit_order(x) for x in dta[2:]))
+           for s, dta in zip(valid["stream"], valid["data"])}
+    sent = [(s, msgs[s, k].tobytes()) for s in range(n_streams) for k in range(n_packets)]
+    back = sum(p in got for p in sent)
+    assert back >= 0.995 * len(sent), f"{back} of {len(sent)} embedded packets recovered"
+    # CRC-valid records that were never sent: chance passes of a 16-bit CRC only
+    extra = len(got - set(sent))
+    assert extra <= 1e-3 * whole.shape[0] + 10, extra
