@@ -42,8 +42,36 @@ __device__ __forceinline__ float s8f(uint32_t x) {
         : "=f"(a) : "r"(x), "n"(8 * B));
     return a;
 }
+#if CONV == 2
+// fp16 route: one PRMT per sample builds (1024 + I, 1024 + Q) as a half pair, a mixed-precision
+// add (float + half, SASS FHADD) centres each component: half the PRMTs, scalar adds
+__device__ float g_k1151 = 1151.0f;
+template <int H, bool NEG>
+__device__ __forceinline__ float centred(uint32_t h2, float k1151) {
+    float r;
+    const unsigned short h = (unsigned short)(H ? (h2 >> 16) : (h2 & 0xFFFFu));
+    if (NEG)
+        asm("{ .reg .b16 t; neg.f16 t, %1; add.rn.f32.f16 %0, t, %2; }" : "=f"(r) : "h"(h), "f"(k1151));
+    else
+        asm("add.rn.f32.f16 %0, %1, %2;" : "=f"(r) : "h"(h), "f"(-k1151));
+    return r;
+}
+#endif
 template <int I>
 __device__ __forceinline__ void conv_pair(uint32_t wa, uint32_t wb, float2 &re, float2 &im) {
+#if CONV == 2
+    {
+        const float k = g_k1151;
+        const uint32_t ha = __byte_perm(wa, 0x64646464u, (I & 1) ? 0x4342 : 0x4140);
+        const uint32_t hb = __byte_perm(wb, 0x64646464u, (I & 1) ? 0x4342 : 0x4140);
+        constexpr int ph = I & 3;
+        if (ph == 0) { re = f2(centred<0, false>(ha, k), centred<0, false>(hb, k)); im = f2(centred<1, false>(ha, k), centred<1, false>(hb, k)); }
+        else if (ph == 1) { re = f2(centred<1, true>(ha, k), centred<1, true>(hb, k)); im = f2(centred<0, false>(ha, k), centred<0, false>(hb, k)); }
+        else if (ph == 2) { re = f2(centred<0, true>(ha, k), centred<0, true>(hb, k)); im = f2(centred<1, true>(ha, k), centred<1, true>(hb, k)); }
+        else { re = f2(centred<1, false>(ha, k), centred<1, false>(hb, k)); im = f2(centred<0, true>(ha, k), centred<0, true>(hb, k)); }
+        return;
+    }
+#endif
 #if CONV == 1
     if ((I & 1) == 0) {          // bytes 0, 1 of the word; XU pipe, no PRMT, no centring add
         const uint32_t xa = wa ^ 0x80808080u, xb = wb ^ 0x80808080u;
