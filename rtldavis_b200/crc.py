@@ -3,7 +3,7 @@
 ``CRC(name, init, poly, residue).checksum(data)`` keeps the reference signature;
 the arithmetic runs in the library's CRC kernel (one launch per call -- this
 entry exists for API parity and parity tests; on the hot path the CRC is fused
-into the confirm kernel and arrives as ``davis_hit.crc_ok``).
+into the slicing kernel and arrives as ``davis_hit.crc_ok``).
 ``checksum_many`` is the batched form.
 """
 from __future__ import annotations

@@ -38,10 +38,11 @@
 //   the filter as a period-4 constant folded into the first FMA.  The rotation phase
 //   is taken relative to the lane's window because a common unit factor cancels in
 //   Im(conj(F[n-1]) F[n]).
-//   Every decision that reaches a caller is re-derived in fp64 by the confirm
-//   kernel, so an fp32 sign that disagrees with the reference's float64 (only
-//   possible when the cross product is ~1e-6 of |F[n-1]||F[n]|) cannot change a
-//   packet.
+//   Every decision that reaches a caller is re-derived by k_exact (davis_search.cu): in
+//   fp32 with an error bound beside it, in the reference's float64 form where the
+//   numerator lies inside the bound.  So an fp32 sign here that disagrees with the
+//   reference's (only possible when the cross product is ~1e-6 of |F[n-1]||F[n]|)
+//   cannot change a packet.
 //
 // Cost model (measured, profiles/r01_demod_lab.txt): FFMA2/FADD2/FMUL2 occupy the FMA
 // pipe 2 cycles per warp instruction and there is one issue slot per cycle.  Per

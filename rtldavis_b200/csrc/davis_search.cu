@@ -1,5 +1,6 @@
-// davis_search.cu -- sync-word search over the decision-bit planes, fp64
-// confirmation, packet slicing, CRC-16 and per-call record generation.
+// davis_search.cu -- sync-word search over the decision bitmap, confirmation of the
+// candidates (guarded fp32 / fp64), packet slicing, CRC-16, per-call dedupe, RSSI/SNR and
+// discriminator mean, ordering of the records, carried state.
 //
 // Replaces Demodulator._search (src/rtldavis/dsp.py:171-188; Go Pack/Search,
 // dsp/dsp.go:105-131 + dsp/search.go:104-119), Demodulator._slice
@@ -12,15 +13,16 @@
 namespace davis {
 
 // ---------------------------------------------------------------------------
-// k_search: one thread per bitmap word (28 sample positions).
+// k_search: one thread per SEARCH_WORDS bitmap words (28 sample positions each).
 // The preamble's symbol i of a position v = 28w + b sits at sample v + 14i, i.e.
 // for even i = 2m at bit b of word w+m, and for odd i = 2m+1 at bit b of the
 // "half-step" word H[m] = (W[w+m] >> 14) | (W[w+m+1] << 14).  So the sixteen
 // comparisons of all 28 positions are sixteen bitwise ops on whole words.
 // A position is a candidate when its 16 symbols differ from the sync word in at
-// most one symbol; a two-bit saturating mismatch counter is kept bit-sliced (two
-// words) so that test, too, is word-parallel and only true candidates (17 in
-// 65536 positions of noise) reach the scalar code.
+// most one symbol.  Stage one keeps the positions where at least three of the four
+// quarters of the sync word match exactly (word-parallel); stage two counts the
+// differing symbols of the survivors exactly, one position per lane, so only true
+// candidates (17 in 65536 positions of noise) reach the list.
 // The one-symbol slack exists because the bitmap comes from fp32 arithmetic: a
 // true match (in the reference's float64) with one marginal fp32 sign must not
 // be lost.  k_precheck settles such positions in fp64.
