@@ -594,3 +594,33 @@ def test_full_size_batch_properties(dsp, protocol):
     # CRC-valid records that were never sent: chance passes of a 16-bit CRC only
     extra = len(got - set(sent))
     assert extra <= 1e-3 * whole.shape[0] + 10, extra
+
+
+# ---------------------------------------------------------------------------
+# shapes: many streams with few blocks, odd stream counts, strided device rows
+# ---------------------------------------------------------------------------
+def test_many_streams_few_blocks_and_strided_rows(dsp, protocol):
+    """4 099 streams (a prime: no grid divides it) x 3 blocks, as rows of a wider device
+    tensor (row stride > row length).  Stream s carries capture s mod 61, so its records
+    must equal those of the oracle for that capture; BASELINE config 4's stream count."""
+    import torch
+    distinct, n_streams, n_blocks = 61, 4099, 3
+    base, _ = _batch(distinct, n_blocks, 25.0, seed0=1300, n_packets=2, df_range_hz=2500.0)
+    want = {}
+    for r in _oracle_rows(base):
+        want.setdefault(r[0], []).append(r[1:])
+    assert sum(len(v) for v in want.values()) >= distinct
+    wide = torch.zeros((n_streams, 2 * n_blocks * 8192 + 4096), dtype=torch.uint8, device="cuda")
+    src = torch.from_numpy(base).cuda()
+    idx = torch.arange(n_streams, device="cuda") % distinct
+    wide[:, : 2 * n_blocks * 8192] = src[idx]
+    view = wide[:, : 2 * n_blocks * 8192]
+    assert view.stride(0) > view.shape[1]
+    with dsp.BatchDemodulator(protocol.new_packet_config(14), n_streams, max_blocks=n_blocks) as bd:
+        bd.submit(view)
+        hits = bd.fetch()
+    got = {}
+    for r in _gpu_rows(hits):
+        got.setdefault(r[0], []).append(r[1:])
+    for s in range(n_streams):
+        assert got.get(s, []) == want.get(s % distinct, []), f"stream {s}"
