@@ -624,3 +624,31 @@ def test_many_streams_few_blocks_and_strided_rows(dsp, protocol):
         got.setdefault(r[0], []).append(r[1:])
     for s in range(n_streams):
         assert got.get(s, []) == want.get(s % distinct, []), f"stream {s}"
+
+
+def test_result_buffer_overflow_is_an_error_not_a_truncation(dsp, protocol):
+    """a hit buffer that is too small is reported, never silently cut."""
+    from rtldavis_b200 import _lib
+    iq, _ = _batch(4, 10, 30.0, seed0=1500, n_packets=6)
+    assert len(_oracle_rows(iq)) > 8
+    bd = dsp.BatchDemodulator(protocol.new_packet_config(14), 4, max_blocks=10, max_hits=8)
+    bd.submit(iq)
+    with pytest.raises(_lib.DavisError) as e:
+        bd.fetch()
+    assert e.value.code == _lib.E_OVERFLOW
+    bd.close()
+    # the same batch with room for everything is fine
+    bd = dsp.BatchDemodulator(protocol.new_packet_config(14), 4, max_blocks=10)
+    bd.submit(iq)
+    assert _gpu_rows(bd.fetch()) == _oracle_rows(iq)
+    # call sequence: a second fetch hands out the same records again; a fetch on a fresh
+    # handle and a second submit before the fetch are errors
+    assert _gpu_rows(bd.fetch()) == _oracle_rows(iq)
+    with dsp.BatchDemodulator(protocol.new_packet_config(14), 4, max_blocks=10) as fresh:
+        with pytest.raises(_lib.DavisError):
+            fresh.fetch()
+    bd.submit(iq)
+    with pytest.raises(_lib.DavisError):
+        bd.submit(iq)
+    bd.fetch()
+    bd.close()
