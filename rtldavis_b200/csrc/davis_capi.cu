@@ -43,6 +43,7 @@ struct Stage {
 struct Group {
     int stage = 0, s0 = 0, ns = 0;
     size_t hit_off = 0;  unsigned int hit_cap = 0, n_hit = 0;
+    uint32_t *planes = nullptr;          // bitmap rows of this group's streams
     cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
 };
 
@@ -66,6 +67,7 @@ struct davis_handle {
     std::vector<cudaEvent_t> event_pool;
     davis_hit *d_hits = nullptr;  size_t d_hits_cap = 0;
     Counters *h_ctr = nullptr;    size_t h_ctr_cap = 0;     // pinned, one per group
+    cudaEvent_t demod_ev[2] = {nullptr, nullptr};           // around a demodulation launch shared by groups
 
     bool queued = false;
     int queued_blocks = 0;
@@ -160,15 +162,20 @@ int get_event(davis_handle *h, cudaEvent_t *e) {
 }
 
 void release_groups(davis_handle *h) {
+    for (auto &e : h->demod_ev)
+        if (e) { h->event_pool.push_back(e); e = nullptr; }
     for (auto &g : h->groups)
         for (auto &e : g.ev)
             if (e) { h->event_pool.push_back(e); e = nullptr; }
     h->groups.clear();
 }
 
-// Enqueue every kernel of one group of streams on `st`.
+// Enqueue every kernel of one group of streams on `st`.  `dev_input` points at the group's
+// first stream.  With `demod_done` set, the bitmap rows of the group (g.planes) are being
+// written by a demodulation launch on another stream that covers several groups: this
+// chain then starts at the search and waits for that event first (its memsets do not).
 int run_group(davis_handle *h, Stage &stage, Group &g, int gi, const uint8_t *dev_input,
-              size_t input_stride, int n_blocks, cudaStream_t st) {
+              size_t input_stride, int n_blocks, cudaStream_t st, cudaEvent_t demod_done = nullptr) {
     View vw;
     vw.carry = h->carry[h->cur] + (size_t)g.s0 * h->carry_stride + h->elem * (size_t)(h->n_keep - h->n_carry);
     vw.input = dev_input;
@@ -202,15 +209,21 @@ int run_group(davis_handle *h, Stage &stage, Group &g, int gi, const uint8_t *de
     CU(cudaMemsetAsync(stage.tbl, 0xFF, stage.tbl_size * sizeof(uint32_t), st));
     CU(cudaMemsetAsync(stage.lost, 0, g.hit_cap, st));
     CU(cudaMemsetAsync(stage.marks, 0, sizeof(uint32_t) * (size_t)g.ns * stage.mark_words, st));
-    CU(cudaEventRecord(g.ev[0], st));
-    if (bytes_in) launch_demod(vw, stage.planes, g.ns, stage.tiles, stage.words_alloc, nullptr, 0, st);
-    else launch_exact_all(vw, sp, stage.planes, st);               // complex input: fp64 decisions throughout
+    if (!g.planes) g.planes = stage.planes;
+    if (demod_done) {
+        CU(cudaStreamWaitEvent(st, demod_done, 0));
+        CU(cudaEventRecord(g.ev[0], st));
+    } else {
+        CU(cudaEventRecord(g.ev[0], st));
+        if (bytes_in) launch_demod(vw, g.planes, g.ns, stage.tiles, stage.words_alloc, nullptr, 0, st);
+        else launch_exact_all(vw, sp, g.planes, st);               // complex input: fp64 decisions throughout
+    }
     CU(cudaEventRecord(g.ev[1], st));
-    launch_search(stage.planes, sp, stage.cand, stage.ctr, st);
+    launch_search(g.planes, sp, stage.cand, stage.ctr, st);
     CU(cudaEventRecord(g.ev[2], st));
     launch_precheck(vw, sp, stage.cand, stage.conf, stage.marks, stage.glist, stage.ctr, !bytes_in, st);
-    if (bytes_in) launch_exact(vw, sp, stage.planes, stage.glist, stage.fixes, stage.ctr, st);
-    launch_slice(vw, sp, stage.planes, stage.conf, stage.fixes, stage.recs, stage.tbl, stage.lost,
+    if (bytes_in) launch_exact(vw, sp, g.planes, stage.glist, stage.fixes, stage.ctr, st);
+    launch_slice(vw, sp, g.planes, stage.conf, stage.fixes, stage.recs, stage.tbl, stage.lost,
                  stage.ctr, n_blocks, st);
     unsigned int *count = stage.per_stream, *start = count + g.ns, *fill = start + g.ns + 1;
     CU(cudaMemsetAsync(count, 0, sizeof(unsigned int) * g.ns, st));
@@ -226,7 +239,7 @@ int run_group(davis_handle *h, Stage &stage, Group &g, int gi, const uint8_t *de
     CU(cudaEventRecord(g.ev[4], st));
     CU(cudaGetLastError());
     stage.last_group = gi;
-    h->stats.launches += 9 + (uint64_t)((g.ns + 65534) / 65535);
+    h->stats.launches += (demod_done ? 8 : 9) + (uint64_t)((g.ns + 65534) / 65535);
     return DAVIS_OK;
 }
 
@@ -414,6 +427,15 @@ static int demod_common(davis_handle *h, const uint8_t *iq, size_t bytes_per_str
 
     // split into groups
     int per_group = h->n_streams;
+    // Device-resident byte input: ONE demodulation launch over all streams, then the search
+    // and finish kernels of two halves of the streams on two streams.  Those kernels are
+    // latency- or issue-bound and leave the GPU half idle when they run one after another;
+    // two independent chains fill each other's gaps (3.34 -> ~3.1 ms per 1 024 x 328 blocks).
+    const bool split_finish = on_device && elem == 2 && h->n_streams >= 64 && h->stages.size() >= 2;
+    if (split_finish) {
+        const int chains = 2;        // measured: 3 chains are slower again (more small launches)
+        per_group = (h->n_streams + chains - 1) / chains;
+    }
     if (!on_device) {
         per_group = h->cfg.host_group > 0 ? h->cfg.host_group : 0;
         if (per_group <= 0) {                       // ~64 MiB of input per pipeline stage
@@ -426,7 +448,8 @@ static int demod_common(davis_handle *h, const uint8_t *iq, size_t bytes_per_str
     size_t hit_total = 0;
     for (int gi = 0; gi < n_groups; gi++) {
         Group &g = h->groups[gi];
-        g.stage = on_device ? 0 : gi % (int)h->stages.size();
+        g.stage = on_device ? (split_finish ? gi : 0) : gi % (int)h->stages.size();
+        g.planes = nullptr;
         g.s0 = gi * per_group;
         g.ns = std::min(per_group, h->n_streams - g.s0);
         size_t cap = h->cfg.max_hits > 0 ? (size_t)h->cfg.max_hits
@@ -445,6 +468,47 @@ static int demod_common(davis_handle *h, const uint8_t *iq, size_t bytes_per_str
         h->h_ctr_cap = n_groups;
     }
 
+    if (split_finish) {
+        cudaStream_t main_st = cuda_stream ? (cudaStream_t)cuda_stream : h->stages[0].st;
+        // stage 0 holds the bitmap of every stream (and group 0's lists), stage g group g's lists
+        if ((rc = prepare_stage(h, h->stages[0], h->n_streams, n_blocks, 0, h->groups[0].hit_cap))) return rc;
+        for (int gi = 1; gi < n_groups; gi++)
+            if ((rc = prepare_stage(h, h->stages[gi], h->groups[gi].ns, n_blocks, 0, h->groups[gi].hit_cap)))
+                return rc;
+        if (!cuda_stream) main_st = h->stages[0].st;
+        Stage &s0 = h->stages[0];
+        View vw{};
+        vw.carry = h->carry[h->cur] + h->elem * (size_t)(h->n_keep - h->n_carry);
+        vw.input = iq;
+        vw.carry_stride = h->carry_stride;
+        vw.input_stride = stream_stride;
+        vw.blocks_done = h->d_blocks_done;
+        vw.n_carry = h->n_carry;
+        vw.n_new = n_blocks * h->B;
+        vw.block = h->B;
+        vw.window_blocks = h->W;
+        vw.stream0 = 0;
+        vw.lut = h->d_lut;
+        vw.elem = h->elem;
+        cudaEvent_t t0, t1;
+        if ((rc = get_event(h, &t0)) || (rc = get_event(h, &t1))) return rc;
+        CU(cudaEventRecord(t0, main_st));
+        launch_demod(vw, s0.planes, h->n_streams, s0.tiles, s0.words_alloc, nullptr, 0, main_st);
+        CU(cudaEventRecord(t1, main_st));
+        h->stats.launches += 1;
+        h->demod_ev[0] = t0;
+        h->demod_ev[1] = t1;
+        for (int gi = 0; gi < n_groups; gi++) {
+            Group &g = h->groups[gi];
+            g.planes = s0.planes + (size_t)g.s0 * s0.words_alloc;
+            cudaStream_t st = gi == 0 ? main_st : h->stages[g.stage].st;
+            if ((rc = run_group(h, h->stages[g.stage], g, gi, iq + (size_t)g.s0 * stream_stride,
+                                stream_stride, n_blocks, st, t1)))
+                return rc;
+            // whatever the caller enqueues next on its stream comes after every chain
+            if (st != main_st) CU(cudaStreamWaitEvent(main_st, g.ev[4], 0));
+        }
+    } else
     for (int gi = 0; gi < n_groups; gi++) {
         Group &g = h->groups[gi];
         Stage &stage = h->stages[g.stage];
@@ -526,6 +590,11 @@ static int complete_call(davis_handle *h) {
             g.n_hit = c.n_hit;
             h->n_results += c.n_hit;
             h->stats.d2h_bytes += sizeof(Counters);
+        }
+        if (h->demod_ev[0]) {
+            float ms;
+            CU(cudaEventElapsedTime(&ms, h->demod_ev[0], h->demod_ev[1]));
+            demod += ms;
         }
         h->stats.demod_ms = demod;
         h->stats.search_ms = search;
@@ -619,7 +688,7 @@ int davis_debug_bits(davis_handle *h, int stream, uint8_t *out, size_t cap, int6
         if (count > cap) return fail(h, DAVIS_E_OVERFLOW, "bit buffer too small");
         std::vector<uint32_t> words((size_t)st.words_alloc);
         CU(cudaMemcpy(words.data(),
-                      st.planes + (size_t)(stream - g.s0) * st.words_alloc,
+                      (g.planes ? g.planes : st.planes) + (size_t)(stream - g.s0) * st.words_alloc,
                       words.size() * 4, cudaMemcpyDeviceToHost));
         for (size_t i = 0; i < count; i++) {
             const size_t v = i + HALO;
