@@ -63,8 +63,8 @@ struct Fix {
     uint32_t stream, word, diff, pad;
 };
 
-constexpr int DEMOD_WARPS = 8;
-constexpr int DEMOD_CTAS_PER_SM = 2;
+constexpr int DEMOD_WARPS = 16;
+constexpr int DEMOD_CTAS_PER_SM = 1;
 
 void launch_demod(const View &vw, uint32_t *words, int n_streams, int tiles, int words_alloc,
                   float *disc_out, size_t disc_stride, cudaStream_t st);
