@@ -19,8 +19,9 @@
 //     per sample (SHF, 1 instruction) -- no compare, no warp vote; word w of a
 //     stream holds samples [28w, 28w+28), bit i = sample 28w+i.  Stepping by one
 //     symbol (14 samples) is a half-word step, which the search kernel exploits;
-//   * a CTA of 8 warps owns a tile of 512 words = 14336 samples = 28 KiB of input.
-//     CTAs are persistent (2 per SM): each walks tiles unit = blockIdx.x, +gridDim.x,
+//   * a CTA of 16 warps owns a tile of 1024 words = 28672 samples = 56 KiB of input.
+//     CTAs are persistent (1 per SM; with 8 warps x 2 CTAs the second CTA was not always
+//     co-resident and the kernel was 4 % slower): each walks tiles unit = blockIdx.x, +gridDim.x,
 //     ... and one elected thread streams the next tiles into shared memory with the
 //     bulk-copy engine (cp.async.bulk + mbarrier, SASS UBLKCP), three tiles in
 //     flight.  The copy's address arithmetic is done by all threads on uniform
