@@ -27,6 +27,25 @@ namespace davis {
 // true match (in the reference's float64) with one marginal fp32 sign must not
 // be lost.  k_precheck settles such positions in fp64.
 // ---------------------------------------------------------------------------
+// Grid of a persistent (grid-stride) kernel: as many CTAs as are resident at once.  A CTA
+// that has to wait for a slot starts when the others are done and leaves the GPU mostly
+// idle while it works through its share (a register file filled to the last register by
+// N CTAs holds N - 1 of them: k_demod).
+template <class K>
+unsigned int resident_grid(K kernel, int threads, size_t smem = 0) {
+    static int sms = 0;
+    if (!sms) {
+        int dev = 0;
+        cudaGetDevice(&dev);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+        if (sms <= 0) sms = 148;
+    }
+    int per_sm = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, threads, smem) != cudaSuccess || per_sm < 1)
+        per_sm = 1;
+    return (unsigned int)(sms * per_sm);
+}
+
 constexpr int SEARCH_THREADS = 256;
 constexpr uint32_t MASK28 = 0x0FFFFFFFu;
 
@@ -246,12 +265,15 @@ void launch_search(const uint32_t *words, const SearchParams &sp, Cand *cand, Co
         SearchParams part = sp;
         part.n_streams = (int)std::min<long long>(per_launch, sp.n_streams - s0);
         const long long total = part.n_streams * quads;
-        const unsigned grid = (unsigned)std::min<long long>((total + SEARCH_THREADS - 1) / SEARCH_THREADS, 148LL * 8);
+        const long long want = (total + SEARCH_THREADS - 1) / SEARCH_THREADS;
         // the Davis sync word 0xCB89 (symbol 0 in bit 0: 0x91D3) has its polarity compiled in
-        if (sp.pat_rev == 0x91D3u)
+        if (sp.pat_rev == 0x91D3u) {
+            const unsigned grid = (unsigned)std::min<long long>(want, resident_grid(k_search<0x91D3u>, SEARCH_THREADS));
             k_search<0x91D3u><<<grid, SEARCH_THREADS, 0, st>>>(words, part, (unsigned int)s0, cand, ctr);
-        else
+        } else {
+            const unsigned grid = (unsigned)std::min<long long>(want, resident_grid(k_search<0u>, SEARCH_THREADS));
             k_search<0u><<<grid, SEARCH_THREADS, 0, st>>>(words, part, (unsigned int)s0, cand, ctr);
+        }
     }
 }
 
@@ -338,7 +360,7 @@ k_precheck(View vw, SearchParams sp, const Cand *__restrict__ cand, Cand *__rest
 void launch_precheck(const View &vw, const SearchParams &sp, const Cand *cand, Cand *conf,
                      uint32_t *marks, uint2 *glist, Counters *ctr, bool bitmap_is_exact,
                      cudaStream_t st) {
-    k_precheck<<<148 * 4, 256, 0, st>>>(vw, sp, cand, conf, marks, glist, ctr, bitmap_is_exact ? 1 : 0);
+    k_precheck<<<resident_grid(k_precheck, 256), 256, 0, st>>>(vw, sp, cand, conf, marks, glist, ctr, bitmap_is_exact ? 1 : 0);
 }
 
 // ---------------------------------------------------------------------------
@@ -531,7 +553,7 @@ k_exact(View vw, SearchParams sp, uint32_t *__restrict__ planes, const uint2 *__
 
 void launch_exact(const View &vw, const SearchParams &sp, uint32_t *planes, const uint2 *glist,
                   Fix *fixes, Counters *ctr, cudaStream_t st) {
-    k_exact<<<148 * 4, EXACT_WARPS * 32, 0, st>>>(vw, sp, planes, glist, fixes, ctr);
+    k_exact<<<resident_grid(k_exact, EXACT_WARPS * 32), EXACT_WARPS * 32, 0, st>>>(vw, sp, planes, glist, fixes, ctr);
 }
 
 // ---------------------------------------------------------------------------
@@ -743,7 +765,7 @@ k_slice(View vw, SearchParams sp, const uint32_t *__restrict__ planes,
 void launch_slice(const View &vw, const SearchParams &sp, const uint32_t *planes,
                   const Cand *conf, const Fix *fixes, Rec *recs, uint32_t *tbl, uint8_t *lost,
                   Counters *ctr, int n_blocks, cudaStream_t st) {
-    k_slice<<<148 * 4, 256, 0, st>>>(vw, sp, planes, conf, fixes, recs, tbl, lost, ctr, n_blocks);
+    k_slice<<<resident_grid(k_slice, 256), 256, 0, st>>>(vw, sp, planes, conf, fixes, recs, tbl, lost, ctr, n_blocks);
 }
 
 // ---------------------------------------------------------------------------
@@ -1091,7 +1113,7 @@ void launch_finalize(const View &vw, const SearchParams &sp, const Rec *recs, co
                      davis_hit *hits, unsigned int *per_stream, Counters *ctr, cudaStream_t st) {
     // fewer warps per CTA for the wider element types: the staged spans share 48 KiB
     if (vw.elem == 2)
-        k_finalize_u8<<<148 * 2, FIN_WARPS * 32, 0, st>>>(vw, sp, recs, lost, hits, per_stream, ctr);
+        k_finalize_u8<<<resident_grid(k_finalize_u8, FIN_WARPS * 32), FIN_WARPS * 32, 0, st>>>(vw, sp, recs, lost, hits, per_stream, ctr);
     else if (vw.elem == 8)
         k_finalize<8, 4><<<148 * 4, 4 * 32, 0, st>>>(vw, sp, recs, lost, hits, per_stream, ctr);
     else
