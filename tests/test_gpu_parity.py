@@ -652,3 +652,22 @@ def test_result_buffer_overflow_is_an_error_not_a_truncation(dsp, protocol):
         bd.submit(iq)
     bd.fetch()
     bd.close()
+
+
+def test_debug_bits_of_a_stream_in_the_second_finish_chain(dsp, protocol):
+    """With >= 64 device-resident streams the search/finish kernels run as two chains over
+    one shared bitmap; the verification tap must find the rows of either half."""
+    import torch
+    iq, _ = _batch(70, 4, 15.0, seed0=1700, n_packets=1)
+    bd = dsp.BatchDemodulator(protocol.new_packet_config(14), 70, max_blocks=4)
+    bd.submit(torch.from_numpy(iq).cuda())
+    assert _gpu_rows(bd.fetch()) == _oracle_rows(iq)
+    for s in (3, 41, 69):
+        first, bits = bd.debug_bits(s)
+        ref = CO.stream_bits(iq[s])
+        lo = max(first, 16)
+        got = bits[lo - first: lo - first + ref.size - lo]
+        # fp32 decisions of the streaming kernel, corrected where packets were read: they may
+        # differ from the float64 bits only at samples with a numerator next to zero
+        assert got.size > 30000 and np.mean(got != ref[lo:lo + got.size]) < 1e-4
+    bd.close()
