@@ -356,7 +356,10 @@ def run_graft(a):
     if os.path.exists(prof):
         try:
             with open(prof) as f:
-                roofline["traffic"] = json.load(f).get("k_demod_dram_bytes_per_launch")
+                cap = json.load(f)
+            # the ncu capture is of the default workload; any other size has no capture
+            if cap.get("algorithmic_bytes_per_launch") == roofline["algorithmic_bytes_per_launch"]:
+                roofline["traffic"] = cap.get("k_demod_dram_bytes_per_launch")
         except Exception:
             pass
 
