@@ -51,7 +51,10 @@ class FanIn:
 
     IDLE = 127          # byte fed for a stream that has ended
 
-    def __init__(self, demod, sources: Sequence[Source], n_blocks: int = 8):
+    def __init__(self, demod, sources: Sequence[Source], n_blocks: int = 8, prefetch: bool = False):
+        """``prefetch``: read chunk i+1 from the sources while the GPU works on chunk i
+        (two pinned buffers).  For files; on a live pipe it would hold the packets of a
+        chunk back until the next chunk has arrived."""
         if len(sources) != demod.n_streams:
             raise ValueError("one source per stream")
         if n_blocks < 1 or n_blocks > demod.max_blocks:
@@ -63,7 +66,10 @@ class FanIn:
         self._own = [isinstance(s, str) for s in sources]
         self.alive = [True] * len(sources)
         self.blocks_read = [0] * len(sources)
-        self._batch = self._pinned((len(sources), n_blocks * self.block_bytes))
+        self.prefetch = bool(prefetch)
+        self._pins: list = []
+        shape = (len(sources), n_blocks * self.block_bytes)
+        self._batches = [self._pinned(shape) for _ in range(2 if self.prefetch else 1)]
 
     def _pinned(self, shape: Tuple[int, int]) -> np.ndarray:
         """Page-locked host buffer from the library (falls back to pageable memory
@@ -73,15 +79,14 @@ class FanIn:
         n = int(shape[0]) * int(shape[1])
         p = C.c_void_p()
         if L.davis_host_alloc(C.byref(p), n) == 0 and p.value:
-            self._pin = (L, p)
+            self._pins.append((L, p))
             buf = (C.c_uint8 * n).from_address(p.value)
             return np.frombuffer(buf, dtype=np.uint8).reshape(shape)
-        self._pin = None
         return np.empty(shape, dtype=np.uint8)
 
-    def fill(self) -> int:
-        """Reads the next chunk of every live source; returns how many blocks the
-        batch holds (the minimum any live source delivered; 0 = all ended)."""
+    def fill(self, slot: int = 0) -> int:
+        """Reads the next chunk of every live source into buffer ``slot``; returns how many
+        blocks the batch holds (the minimum any live source delivered; 0 = all ended)."""
         step = self.block_bytes
         got: List[Optional[np.ndarray]] = []
         usable = self.n_blocks
@@ -102,7 +107,7 @@ class FanIn:
             return 0
         # every stream advances by the same number of blocks per call
         for i, g in enumerate(got):
-            row = self._batch[i, : usable * step]
+            row = self._batches[slot][i, : usable * step]
             if g is None:
                 row[:] = self.IDLE
             else:
@@ -122,12 +127,19 @@ class FanIn:
 
     def run(self) -> Iterator[np.ndarray]:
         """Yields the packet records of every chunk until all sources end."""
-        while True:
-            n = self.fill()
-            if n == 0:
-                return
-            self.demod.submit(self._batch[:, : n * self.block_bytes])
-            yield self.demod.fetch()
+        slot = 0
+        n = self.fill(slot)
+        while n:
+            self.demod.submit(self._batches[slot][:, : n * self.block_bytes])
+            if self.prefetch:
+                # the other buffer: this one is being copied to the device until fetch() returns
+                slot ^= 1
+                nxt = self.fill(slot)
+                yield self.demod.fetch()
+                n = nxt
+            else:
+                yield self.demod.fetch()
+                n = self.fill(slot)
 
     def close(self) -> None:
         for f, own in zip(self._files, self._own):
@@ -136,11 +148,10 @@ class FanIn:
                     f.close()
                 except Exception:
                     pass
-        if getattr(self, "_pin", None):
-            L, p = self._pin
-            self._batch = None
+        self._batches = []
+        while self._pins:
+            L, p = self._pins.pop()
             L.davis_host_free(p)
-            self._pin = None
 
 
 class _Chain:

@@ -52,11 +52,12 @@ def test_read_exact_and_iter_blocks_short_reads_and_tail():
     assert list(ingest.iter_blocks(io.BytesIO(b""), 16)) == []
 
 
-def test_fan_in_ragged_sources_keep_stream_index_and_order():
+@pytest.mark.parametrize("prefetch", [False, True])
+def test_fan_in_ragged_sources_keep_stream_index_and_order(prefetch):
     step = 32
     a, b, c = _bytes(step * 7, 2), _bytes(step * 3 + 5, 3), _bytes(step * 5, 4)
     rec = _Recorder(3)
-    fan = ingest.FanIn(rec, [io.BytesIO(a), _Dribble(b), io.BytesIO(c)], n_blocks=2)
+    fan = ingest.FanIn(rec, [io.BytesIO(a), _Dribble(b), io.BytesIO(c)], n_blocks=2, prefetch=prefetch)
     assert list(fan.run()) == list(range(1, len(rec.batches) + 1))
     fan.close()
     per_stream = [b"".join(x[i].tobytes() for x in rec.batches) for i in range(3)]
@@ -75,7 +76,8 @@ def test_fan_in_argument_checks():
 
 
 @pytest.mark.gpu
-def test_fan_in_files_equal_direct_submit_and_parse(tmp_path):
+@pytest.mark.parametrize("prefetch", [False, True])
+def test_fan_in_files_equal_direct_submit_and_parse(tmp_path, prefetch):
     from rtldavis_b200 import dsp, protocol
     names = ["hi_snr_8192", "lo_snr_8192"]
     caps = [np.asarray(load_golden(n)["iq"], dtype=np.uint8).ravel() for n in names]
@@ -90,7 +92,7 @@ def test_fan_in_files_equal_direct_submit_and_parse(tmp_path):
         direct.submit(np.stack([c[: n_blocks * 16384] for c in caps]))
         want = direct.fetch()
     with dsp.BatchDemodulator(cfg, 2, max_blocks=8) as bd:
-        fan = ingest.FanIn(bd, paths, n_blocks=5)
+        fan = ingest.FanIn(bd, paths, n_blocks=5, prefetch=prefetch)
         got = np.concatenate(list(fan.run()))
         fan.close()
     key = lambda h: (int(h["stream"]), int(h["call"]), int(h["index"]), h["data"].tobytes(),
