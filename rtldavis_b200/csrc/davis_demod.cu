@@ -242,11 +242,14 @@ k_demod(View vw, uint32_t *__restrict__ words, int words_alloc, int tiles, int n
         __syncwarp();
         if ((threadIdx.x & 31) == 0) mbar_arrive(empty);          // this warp is done with the buffer
         {                                                        // refill it for DEMOD_STAGES tiles ahead
-            const bool more = ps < n_streams;
-            const TileSpan sp = tile_span(vw, more ? ps : 0, pj);
-            if (producer && more) {
-                mbar_wait(empty, parity);
-                issue_tile(sp, smem_addr(buf + slot * BUF_BYTES), full);
+            // only the producer's warp works out the span (a warp-uniform branch: the other
+            // 15 warps skip ~60 index instructions per tile)
+            if (threadIdx.x < 32 && ps < n_streams) {
+                const TileSpan sp = tile_span(vw, ps, pj);
+                if (producer) {
+                    mbar_wait(empty, parity);
+                    issue_tile(sp, smem_addr(buf + slot * BUF_BYTES), full);
+                }
             }
             ps += step_s; pj += step_j;
             if (pj >= tiles) { pj -= tiles; ps++; }
