@@ -244,15 +244,17 @@ k_demod(View vw, uint32_t *__restrict__ words, int words_alloc, int tiles, int n
         {                                                        // refill it for DEMOD_STAGES tiles ahead
             // only the producer's warp works out the span (a warp-uniform branch: the other
             // 15 warps skip ~60 index instructions per tile)
-            if (threadIdx.x < 32 && ps < n_streams) {
-                const TileSpan sp = tile_span(vw, ps, pj);
-                if (producer) {
-                    mbar_wait(empty, parity);
-                    issue_tile(sp, smem_addr(buf + slot * BUF_BYTES), full);
+            if (threadIdx.x < 32) {
+                if (ps < n_streams) {
+                    const TileSpan sp = tile_span(vw, ps, pj);
+                    if (producer) {
+                        mbar_wait(empty, parity);
+                        issue_tile(sp, smem_addr(buf + slot * BUF_BYTES), full);
+                    }
                 }
+                ps += step_s; pj += step_j;
+                if (pj >= tiles) { pj -= tiles; ps++; }
             }
-            ps += step_s; pj += step_j;
-            if (pj >= tiles) { pj -= tiles; ps++; }
         }
 
         // re/im[i] = rotated sample of window index i (V sample 28t - 12 + i), i = 2..38
