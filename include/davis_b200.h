@@ -32,7 +32,7 @@ extern "C" {
 #define DAVIS_API
 #endif
 
-#define DAVIS_ABI_VERSION 1
+#define DAVIS_ABI_VERSION 2
 
 enum {
     DAVIS_OK = 0,
@@ -61,7 +61,22 @@ typedef struct davis_cfg {
     int32_t max_hits;          /* capacity of the per-call packet buffer; 0 = auto  */
     int32_t host_slots;        /* pipeline depth for host-memory input; 0 = auto    */
     int32_t host_group;        /* streams per pipeline stage for host input; 0=auto */
+    int32_t flavor;            /* DAVIS_FLAVOR_PYTHON (0) or DAVIS_FLAVOR_GO (1), ABI >= 2 */
 } davis_cfg;
+
+/* Which of the reference's two implementations the numbers follow where they differ.
+ * Decision bits, packets, the CRC verdict, rssi and snr are the same in both.
+ *   PYTHON: discriminator denominator |a|^2 + 1e-10 (src/rtldavis/dsp.py:88);
+ *           davis_hit.disc_mean = mean(discriminated[index : index+224])
+ *           (src/rtldavis/protocol.py:304-310).
+ *   GO:     denominator |a|^2, no epsilon (dsp/dsp.go:93; 0/0 gives NaN);
+ *           davis_hit.disc_mean = mean(Discriminated[Idx+8*14 : Idx+24*14])
+ *           (protocol/protocol.go:156-164; the caller adds the 9600 Hz bias of
+ *           protocol.go:168).  Use block_size 512 (dsp/dsp.go:212).  Two bits are not
+ *           Go's on amd64: the decisions of global samples 0 and 1 of a fresh stream are
+ *           0/0 in Go, a NaN whose sign bit is platform-defined (set on amd64, clear on
+ *           arm64); this library keeps 0 there, as Python and arm64 do. */
+enum { DAVIS_FLAVOR_PYTHON = 0, DAVIS_FLAVOR_GO = 1 };
 
 /* dsp.Packet, src/rtldavis/dsp.py:12-17 (Go: dsp/dsp.go:133-136), plus the
  * verdict of the CRC gate in Parser.parse, src/rtldavis/protocol.py:290-300, and
@@ -76,7 +91,8 @@ typedef struct davis_hit {
     uint8_t flags;        /* bit0: a decision bit was corrected by the fp64 re-check */
     double rssi;          /* Packet.rssi, dsp.py:207-229                            */
     double snr;           /* Packet.snr,  dsp.py:230-236                            */
-    double disc_mean;     /* mean(discriminated[index:index+224]), protocol.py:304-310;
+    double disc_mean;     /* mean(discriminated[index:index+224]), protocol.py:304-310
+                             (flavor GO: [index+112:index+336], protocol.go:156-164);
                              NaN when crc_ok == 0 (the reference takes it after the CRC gate) */
 } davis_hit;
 

@@ -15,6 +15,12 @@ Two formulations of the same arithmetic live here:
   every preamble position ``g`` is mapped back onto the reference's calls.
   The tests prove both produce identical packet lists.
 
+The Go mirror (:class:`GoCallOracle`, :func:`go_freq_error`) is restated from
+``dsp/dsp.go`` and ``protocol/protocol.go``.  PARITY UNPINNED for that part: there is
+no Go toolchain in the build container, so no output of the Go code itself exists to
+check it against; it shares every stage but FIR summation order and the discriminator
+epsilon with the pinned Python restatement.
+
 Reference citations are ``file:line`` under ``/root/reference``.
 """
 from __future__ import annotations
@@ -238,9 +244,9 @@ class CallOracle:
 
         r = rotate_quarter(x)                                          # dsp.py:160
         iq = np.concatenate([self.tail9, r])                           # dsp.py:154,159
-        f_new = fir9_valid(iq, B)                                      # dsp.py:161
+        f_new = self._fir(iq, B)                                       # dsp.py:161
         f = np.concatenate([self.filtered[-1:], f_new])                # dsp.py:155
-        d_new = discriminate(f)                                        # dsp.py:162
+        d_new = self._disc(f)                                          # dsp.py:162
         self.tail9 = iq[-9:].copy()
         self.filtered = f
         self.discriminated = np.concatenate([self.discriminated[B:], d_new])
@@ -249,6 +255,9 @@ class CallOracle:
         out = self._slice(self._search())
         self.calls += 1
         return out
+
+    _fir = staticmethod(fir9_valid)
+    _disc = staticmethod(discriminate)
 
     # dsp.py:171-188 -- every occurrence, offset-major then ascending
     def _search(self) -> List[int]:
@@ -295,6 +304,63 @@ class CallOracle:
         rssi = 10 * math.log10(power) if power > 0 else -120
         snr = 10 * math.log10(power / noise) if noise > 0 else 50
         return rssi, snr
+
+
+# --------------------------------------------------------------------------
+# the Go mirror (parity unpinned, see the module header)
+# --------------------------------------------------------------------------
+def go_fir9(iq: np.ndarray, n_out: int) -> np.ndarray:
+    """FIR9, dsp/dsp.go:65-83: symmetric taps folded, pairs added before the multiply."""
+    c = FIR_TAPS
+    w = [iq[m:m + n_out] for m in range(9)]
+    acc = (w[0] + w[8]) * c[0]
+    acc = acc + (w[1] + w[7]) * c[1]
+    acc = acc + (w[2] + w[6]) * c[2]
+    acc = acc + (w[3] + w[5]) * c[3]
+    acc = acc + w[4] * c[4]
+    return acc
+
+
+def go_discriminate(f: np.ndarray) -> np.ndarray:
+    """Discriminate, dsp/dsp.go:85-95: no epsilon; 0/0 (zero history) is NaN."""
+    a, b = f[:-1], f[1:]
+    with np.errstate(invalid="ignore", divide="ignore"):
+        return (a.imag * b.real - a.real * b.imag) / (a.real * a.real + a.imag * a.imag)
+
+
+def go_quantize(d: np.ndarray) -> np.ndarray:
+    """Quantize, dsp/dsp.go:97-103: bit 63.  The NaN of 0/0 has a platform-defined sign
+    (set on amd64, clear on arm64); it is taken as clear here (the samples this
+    touches are global samples 0 and 1 of a fresh stream)."""
+    return np.where(np.isnan(d), 0, np.signbit(d)).astype(np.uint8)
+
+
+class GoCallOracle(CallOracle):
+    """Demodulator.Demodulate, dsp/dsp.go:271-291 (block size 512, dsp.go:212).  Pack +
+    Search (dsp.go:105-131,258-265) look only at the first block_size + preamble_length
+    samples, which is every position Slice keeps (dsp.go:148: qIdx <= BlockSize); RSSI/SNR
+    do not exist in Go and are whatever the Python formula gives."""
+
+    def __init__(self, cfg: OracleConfig = OracleConfig(block_size=512)):
+        super().__init__(cfg)
+        self._quant = go_quantize
+
+    _fir = staticmethod(go_fir9)
+    _disc = staticmethod(go_discriminate)
+
+
+def go_freq_error(discriminated: np.ndarray, index: int, cfg: OracleConfig):
+    """Parser.Parse, protocol/protocol.go:154-168: mean over symbols 8..24 after the
+    preamble index, then -int(9600 + mean * Fs / 2 pi).  Returns (mean, error); error is
+    None when the mean is NaN (Go's int(NaN) is platform-defined)."""
+    import math
+    lower = index + 8 * cfg.symbol_length
+    upper = index + 24 * cfg.symbol_length
+    tail = discriminated[lower:upper]
+    mean = float(np.sum(tail) / len(tail)) if not np.isnan(tail).any() else float("nan")
+    if math.isnan(mean):
+        return mean, None
+    return mean, -int(9600 + (mean * float(cfg.sample_rate)) / (2 * math.pi))
 
 
 def run_calls(u8: np.ndarray, cfg: OracleConfig = OracleConfig(),

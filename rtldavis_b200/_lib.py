@@ -20,7 +20,8 @@ class DavisCfg(C.Structure):
                 ("preamble_symbols", C.c_int32), ("packet_symbols", C.c_int32),
                 ("preamble", C.c_uint32), ("block_size", C.c_int32),
                 ("max_blocks", C.c_int32), ("max_hits", C.c_int32),
-                ("host_slots", C.c_int32), ("host_group", C.c_int32)]
+                ("host_slots", C.c_int32), ("host_group", C.c_int32),
+                ("flavor", C.c_int32)]
 
 
 class DavisStats(C.Structure):
@@ -97,7 +98,7 @@ def load() -> C.CDLL:
         fn = getattr(L, name)
         if fn.restype is C.c_int or fn.restype is None:
             fn.restype = i32
-    if L.davis_abi_version() != 1:
+    if L.davis_abi_version() != 2:
         raise ImportError("libdavis_b200.so ABI version mismatch")
     _lib = L
     return L

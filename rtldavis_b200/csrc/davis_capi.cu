@@ -80,6 +80,13 @@ struct davis_handle {
 
 namespace {
 
+// davis_cfg.flavor -> the two places where the Go mirror's numbers differ (include/davis_b200.h)
+void set_flavor(const davis_handle *h, View *vw) {
+    const bool go = h->cfg.flavor == DAVIS_FLAVOR_GO;
+    vw->disc_eps = go ? 0.0 : 1e-10;                 // dsp/dsp.go:93 vs dsp.py:88
+    vw->disc_off = go ? 8 * SPS : 0;                 // protocol/protocol.go:156 vs protocol.py:305
+}
+
 double now_ms() {
     return std::chrono::duration<double, std::milli>(
                std::chrono::steady_clock::now().time_since_epoch()).count();
@@ -189,6 +196,7 @@ int run_group(davis_handle *h, Stage &stage, Group &g, int gi, const uint8_t *de
     vw.stream0 = g.s0;
     vw.lut = h->d_lut;
     vw.elem = h->elem;
+    set_flavor(h, &vw);
     const bool bytes_in = h->elem == 2;
 
     SearchParams sp;
@@ -269,7 +277,8 @@ int davis_create(const davis_cfg *cfg, int n_streams, int device, davis_handle *
     *out = nullptr;
     if (cfg->symbol_length != SPS || cfg->preamble_symbols != PRE_SYMS ||
         cfg->packet_symbols != PKT_SYMS || cfg->block_size < 256 || cfg->block_size % 8 ||
-        cfg->max_blocks < 1 || cfg->preamble > 0xFFFFu)
+        cfg->max_blocks < 1 || cfg->preamble > 0xFFFFu ||
+        (cfg->flavor != DAVIS_FLAVOR_PYTHON && cfg->flavor != DAVIS_FLAVOR_GO))
         return DAVIS_E_INVAL;
     int count = 0;
     if (cudaGetDeviceCount(&count) != cudaSuccess || device < 0 || device >= count)
@@ -490,6 +499,7 @@ static int demod_common(davis_handle *h, const uint8_t *iq, size_t bytes_per_str
         vw.stream0 = 0;
         vw.lut = h->d_lut;
         vw.elem = h->elem;
+        set_flavor(h, &vw);
         cudaEvent_t t0, t1;
         if ((rc = get_event(h, &t0)) || (rc = get_event(h, &t1))) return rc;
         CU(cudaEventRecord(t0, main_st));
@@ -712,6 +722,7 @@ static int debug_view(davis_handle *h, View *vw) {
     vw->stream0 = 0;
     vw->lut = h->d_lut;
     vw->elem = h->elem;
+    set_flavor(h, vw);
     return DAVIS_OK;
 }
 

@@ -49,6 +49,11 @@ struct View {
     int stream0;              // first stream of this pipeline stage (for records)
     const double *lut;        // device copy of the float64 byte->sample table (256 entries)
     int elem;                 // bytes per sample: 2 (uint8 I,Q), 8 (complex64) or 16 (complex128)
+    // davis_cfg.flavor: the Python discriminator adds 1e-10 to |a|^2 (dsp.py:88), the Go one
+    // adds nothing (dsp/dsp.go:93); the parser's mean starts at index (protocol.py:304-308)
+    // or 8 symbols later (protocol/protocol.go:156-158)
+    double disc_eps;
+    int disc_off;
 };
 
 // copy the table into shared memory (call from every thread of the block)
@@ -306,9 +311,9 @@ __device__ __forceinline__ double exact_cross(const Cplx &a, const Cplx &b) {
     return __dsub_rn(__dmul_rn(a.im, b.re), __dmul_rn(a.re, b.im));
 }
 
-// D[g] = cross / (|a|^2 + 1e-10)
-__device__ __forceinline__ double exact_disc_from(const Cplx &a, const Cplx &b) {
-    const double den = __dadd_rn(__dadd_rn(__dmul_rn(a.re, a.re), __dmul_rn(a.im, a.im)), 1e-10);
+// D[g] = cross / (|a|^2 + eps), eps = 1e-10 (Python) or 0 (Go: 0/0 stays a NaN)
+__device__ __forceinline__ double exact_disc_from(const Cplx &a, const Cplx &b, double eps) {
+    const double den = __dadd_rn(__dadd_rn(__dmul_rn(a.re, a.re), __dmul_rn(a.im, a.im)), eps);
     return __ddiv_rn(exact_cross(a, b), den);
 }
 
@@ -334,11 +339,11 @@ __device__ __forceinline__ void exact_pair(const double *lut, const Src &src, in
 }
 
 template <class Src>
-__device__ __forceinline__ double exact_disc(const double *lut, const Src &src, int v) {
+__device__ __forceinline__ double exact_disc(const double *lut, const Src &src, int v, double eps) {
     if (src.g0 + v < 0) return 0.0;              // untouched zero buffer
     Cplx a, b;
     exact_pair(lut, src, v, a, b);
-    return exact_disc_from(a, b);
+    return exact_disc_from(a, b, eps);
 }
 
 // quantize: IEEE sign bit of D[g].  The denominator is positive and finite, so

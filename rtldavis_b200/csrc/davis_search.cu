@@ -794,14 +794,14 @@ __device__ double power_sum(const double *lut, const Src &src, int v0, int v1, i
 
 // sum of D[v] over [v0, v0 + 32 * FIN_CHUNK)
 template <class Src>
-__device__ double disc_sum(const double *lut, const Src &src, int v0, int lane) {
+__device__ double disc_sum(const double *lut, const Src &src, int v0, int lane, double eps) {
     const int a = v0 + FIN_CHUNK * lane;
     Cplx F[FIN_CHUNK + 1];
     filtered_run<FIN_CHUNK + 1>(lut, src, a - 1, F);
     double acc = 0.0;
 #pragma unroll
     for (int k = 0; k < FIN_CHUNK; k++)
-        acc += (src.g0 + a + k < 0) ? 0.0 : exact_disc_from(F[k], F[k + 1]);
+        acc += (src.g0 + a + k < 0) ? 0.0 : exact_disc_from(F[k], F[k + 1], eps);
     return warp_sum(acc);
 }
 
@@ -839,14 +839,14 @@ k_finalize(View vw, SearchParams sp, const Rec *__restrict__ recs,
                                         reinterpret_cast<uint8_t *>(mem_p[warp]), lane);
         // protocol.py:304-310: discriminated[] spans the window's last two blocks;
         // discriminated[i] = D[(call-1)*B + i], V index w0 + (W-2)*B + i.
-        const int d0 = w0 + (vw.window_blocks - 2) * B + q;
+        const int d0 = w0 + (vw.window_blocks - 2) * B + q + vw.disc_off;
         const SpanSrcT<ES> sp_d = stage_span<ES>(vw, s, d0 - 11, PRE + 11,
                                         reinterpret_cast<uint8_t *>(mem_d[warp]), lane);
         const double sig = power_sum(lut, sp_p, f0 + q, f0 + s1, lane) / (double)(s1 - q);
         const double noise = q > n0 ? power_sum(lut, sp_p, f0 + n0, f0 + q, lane) / (double)(q - n0)
                                     : 1e-9;
         // protocol.py:297-310: only a packet that passes the CRC gate has its mean taken
-        const double dsum = r.crc_ok ? disc_sum(lut, sp_d, d0, lane) : 0.0;
+        const double dsum = r.crc_ok ? disc_sum(lut, sp_d, d0, lane, vw.disc_eps) : 0.0;
         if (lane == 0) {
             const unsigned int at = atomicAdd(&ctr->n_hit, 1u);   // <= n_rec <= hit_cap
             atomicAdd(&per_stream[s], 1u);
@@ -935,7 +935,8 @@ __device__ __forceinline__ double int_power_sum(const uint8_t *base, int vb, int
 }
 
 // sum of D[v] over [v0, v0 + 224)
-__device__ __forceinline__ double int_disc_sum(const uint8_t *base, int vb, int v0, int lane) {
+__device__ __forceinline__ double int_disc_sum(const uint8_t *base, int vb, int v0, int lane,
+                                               double eps) {
     const int a = v0 + FIN_CHUNK * lane;
     Cplx F[FIN_CHUNK + 1];
     int_filtered_run<FIN_CHUNK + 1>(base + 2 * (a - 10 - vb), F);
@@ -943,7 +944,7 @@ __device__ __forceinline__ double int_disc_sum(const uint8_t *base, int vb, int 
 #pragma unroll
     for (int k = 0; k < FIN_CHUNK; k++) {
         const double num = F[k].im * F[k + 1].re - F[k].re * F[k + 1].im;
-        const double den = fma(F[k].re, F[k].re, fma(F[k].im, F[k].im, 1e-10 * LUT_SCALE2));
+        const double den = fma(F[k].re, F[k].re, fma(F[k].im, F[k].im, eps * LUT_SCALE2));
         double rcp;
         asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(rcp) : "d"(den));   // ~20 bits; two Newton steps
         rcp = fma(rcp, fma(-den, rcp, 1.0), rcp);
@@ -983,7 +984,7 @@ __device__ __forceinline__ FinGeom fin_geom(const View &vw, uint32_t stream, int
     g.s1 = min(q + PRE, B + 1);                                // slice end is clipped by numpy
     g.n0 = max(0, q - PRE);
     // protocol.py:304-310: discriminated[i] = D[(call-1)*B + i]
-    g.d0 = w0 + (vw.window_blocks - 2) * B + q;
+    g.d0 = w0 + (vw.window_blocks - 2) * B + q + vw.disc_off;
     return g;
 }
 struct FinFetch { uint4 p0, p1, d; int64_t done; };
@@ -1073,11 +1074,11 @@ k_finalize_u8(View vw, SearchParams sp, const Rec *__restrict__ recs,
                 sp_d.base = bd; sp_d.v0 = dvb; sp_d.g0 = g0;
                 sig = power_sum(lut, sp_p, g.f0 + q, g.f0 + g.s1, lane);
                 noise = q > g.n0 ? power_sum(lut, sp_p, g.f0 + g.n0, g.f0 + q, lane) : 0.0;
-                if (want_disc) dsum = disc_sum(lut, sp_d, g.d0, lane);
+                if (want_disc) dsum = disc_sum(lut, sp_d, g.d0, lane, vw.disc_eps);
             } else {
                 sig = int_power_sum(bp, pvb, g.f0 + q, g.f0 + g.s1, lane) * (1.0 / LUT_SCALE2);
                 noise = q > g.n0 ? int_power_sum(bp, pvb, g.f0 + g.n0, g.f0 + q, lane) * (1.0 / LUT_SCALE2) : 0.0;
-                if (want_disc) dsum = int_disc_sum(bd, dvb, g.d0, lane);
+                if (want_disc) dsum = int_disc_sum(bd, dvb, g.d0, lane, vw.disc_eps);
             }
             sig /= (double)(g.s1 - q);
             noise = q > g.n0 ? noise / (double)(q - g.n0) : 1e-9;
@@ -1277,7 +1278,7 @@ __global__ void k_exact_disc(View vw, int stream, int v0, int n, double *out) {
     __shared__ double lut[256];
     stage_lut(lut, vw.lut);
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) out[i] = exact_disc(lut, GlobalSrcT<ES>(vw, stream), v0 + i);
+    if (i < n) out[i] = exact_disc(lut, GlobalSrcT<ES>(vw, stream), v0 + i, vw.disc_eps);
 }
 
 void launch_exact_disc(const View &vw, int stream, int v0, int n, double *out, cudaStream_t st) {

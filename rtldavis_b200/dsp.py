@@ -33,10 +33,21 @@ class Packet:
 
 
 class PacketConfig:
-    """dsp.PacketConfig, src/rtldavis/dsp.py:101-125 (same derived attributes)."""
+    """dsp.PacketConfig, src/rtldavis/dsp.py:101-125 (same derived attributes).
+
+    ``flavor`` is not in the reference: ``"python"`` (default) follows src/rtldavis,
+    ``"go"`` follows the Go mirror where its numbers differ -- no epsilon in the
+    discriminator (dsp/dsp.go:93) and the parser's mean taken over symbols 8..24
+    (protocol/protocol.go:156-164); pair it with ``block_size=512`` (dsp/dsp.go:212)."""
+
+    FLAVORS = {"python": 0, "go": 1}
 
     def __init__(self, bit_rate: int, symbol_length: int, preamble_symbols: int,
-                 packet_symbols: int, preamble: str, block_size: int = 512) -> None:
+                 packet_symbols: int, preamble: str, block_size: int = 512,
+                 flavor: str = "python") -> None:
+        if flavor not in self.FLAVORS:
+            raise ValueError("flavor must be 'python' or 'go'")
+        self.flavor = flavor
         self.bit_rate = bit_rate
         self.symbol_length = symbol_length
         self.preamble_symbols = preamble_symbols
@@ -57,7 +68,8 @@ class PacketConfig:
             raise ValueError("preamble must be a string of preamble_symbols 0/1 characters")
         return DavisCfg(self.bit_rate, self.symbol_length, self.preamble_symbols,
                         self.packet_symbols, int(self.preamble, 2), self.block_size,
-                        max_blocks, max_hits, host_slots, host_group)
+                        max_blocks, max_hits, host_slots, host_group,
+                        self.FLAVORS[self.flavor])
 
 
 def _device_pointer(x):

@@ -6,13 +6,13 @@ class DavisCfg(C.Structure):
     _fields_ = [(n, C.c_int32) for n in ("bit_rate", "symbol_length", "preamble_symbols",
                 "packet_symbols")] + [("preamble", C.c_uint32)] + \
                [(n, C.c_int32) for n in ("block_size", "max_blocks", "max_hits",
-                "host_slots", "host_group")]
+                "host_slots", "host_group", "flavor")]    # flavor: 0 Python, 1 Go
 
 HIT = np.dtype([("position", "<i8"), ("stream", "<u4"), ("call", "<u4"), ("index", "<i4"),
                 ("data", "u1", (10,)), ("crc_ok", "u1"), ("flags", "u1"),
                 ("rssi", "<f8"), ("snr", "<f8"), ("disc_mean", "<f8")])       # 56 bytes
 
-cfg = DavisCfg(19200, 14, 16, 80, 0xCB89, 8192, 1, 0, 0, 0)
+cfg = DavisCfg(19200, 14, 16, 80, 0xCB89, 8192, 1, 0, 0, 0, 0)
 h = C.c_void_p()
 assert L.davis_create(C.byref(cfg), 1, 0, C.byref(h)) == 0
 
