@@ -233,7 +233,7 @@ def run_reference(a):
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
     return 0
 
 
@@ -430,7 +430,7 @@ def run_graft(a):
             "valid_packets_per_step": int(n_valid.item()),
             "embedded_packets_per_step": a.streams * a.packets * world,
         }
-        print(json.dumps(line), flush=True)
+        emit(line)
     bd.close()
     bd_b.close()
     if world > 1:
@@ -438,8 +438,27 @@ def run_graft(a):
     return 0
 
 
+_JSON_FD = None
+
+
+def emit(line: dict) -> None:
+    """The ONE stdout line of the contract."""
+    data = (json.dumps(line) + "\n").encode()
+    if _JSON_FD is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_JSON_FD, data)
+
+
 def main():
+    global _JSON_FD
     a = parse_args()
+    # Libraries write to fd 1 behind Python's back (NCCL prints "NCCL version ..." there on
+    # rank 0 when the box sets NCCL_DEBUG): everything but the JSON line goes to stderr.
+    sys.stdout.flush()
+    _JSON_FD = os.dup(1)
+    os.dup2(2, 1)
     if a.impl == "reference":
         return run_reference(a)
     return run_graft(a)
