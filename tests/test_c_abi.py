@@ -32,7 +32,7 @@ def test_library_loads_and_exports_every_declared_symbol():
     missing = [n for n in _declared() if not hasattr(L, n)]
     assert not missing, f"declared in include/davis_b200.h but not exported: {missing}"
     L.davis_abi_version.restype = C.c_int
-    assert L.davis_abi_version() >= 1
+    assert L.davis_abi_version() == 2          # davis_cfg.flavor was added in version 2
     L.davis_strerror.restype = C.c_char_p
     assert L.davis_strerror(0) is not None
 
@@ -42,6 +42,21 @@ def test_struct_layouts_match_the_python_mirror():
     # davis_hit: int64, 3 x 32-bit, 10 + 2 bytes, 3 doubles = 56 bytes (include/davis_b200.h)
     assert dsp.HIT_DTYPE.itemsize == 56
     assert dsp.HIT_DTYPE.fields["data"][1] == 20 and dsp.HIT_DTYPE.fields["rssi"][1] == 32
+
+
+def test_davis_cfg_layout_and_argument_checks_need_no_gpu():
+    """davis_create validates the configuration before it touches CUDA: a flavor (or a
+    symbol length) the library does not implement is DAVIS_E_INVAL on any machine."""
+    from rtldavis_b200 import _lib
+    L = _lib.load()
+    assert C.sizeof(_lib.DavisCfg) == 44                       # eleven 32-bit fields
+    assert _lib.DavisCfg.flavor.offset == 40
+    h = C.c_void_p()
+    bad_flavor = _lib.DavisCfg(19200, 14, 16, 80, 0xCB89, 8192, 1, 0, 0, 0, 7)
+    assert L.davis_create(C.byref(bad_flavor), 1, 0, C.byref(h)) == _lib.E_INVAL and not h.value
+    bad_sps = _lib.DavisCfg(19200, 13, 16, 80, 0xCB89, 8192, 1, 0, 0, 0, 0)
+    assert L.davis_create(C.byref(bad_sps), 1, 0, C.byref(h)) == _lib.E_INVAL
+    assert L.davis_create(None, 1, 0, C.byref(h)) == _lib.E_INVAL
 
 
 def _no_gpu():
