@@ -1,6 +1,6 @@
 #!/usr/bin/env python3
 """Randomised parity soak: random stream counts, block counts, SNRs, chunkings, host/device input,
-every record against the C oracle.  Usage: python tools/fuzz_parity.py [cases] [seed]"""
+every record against the C oracle.  Usage: python tests/fuzz_parity.py [cases] [seed]"""
 import os, sys, time
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np
@@ -14,7 +14,6 @@ def rows(h):
 def main():
     cases = int(sys.argv[1]) if len(sys.argv) > 1 else 30
     rng = np.random.default_rng(int(sys.argv[2]) if len(sys.argv) > 2 else 1)
-    cfg = protocol.new_packet_config(14)
     t0 = time.time()
     total = 0
     for c in range(cases):
@@ -31,6 +30,12 @@ def main():
             step = int(rng.integers(1, nb - k + 1))
             cuts.append(step); k += step
         on_dev = bool(rng.integers(0, 2))
+        # the flavor (davis_cfg.flavor) must not change a record: one case in three runs as Go
+        go = c % 3 == 2
+        if go:
+            cfg = dsp.PacketConfig(19200, 14, 16, 80, "1100101110001001", block_size=8192, flavor="go")
+        else:
+            cfg = protocol.new_packet_config(14)
         bd = dsp.BatchDemodulator(cfg, ns, max_blocks=max(cuts))
         got, k = [], 0
         for step in cuts:
@@ -41,7 +46,7 @@ def main():
         bd.close()
         ok = sorted(got) == sorted(want)
         total += len(want)
-        print(f"case {c:3d}: streams {ns:4d} blocks {nb:2d} snr {snr:5.1f} cuts {cuts} {'dev' if on_dev else 'host'} "
+        print(f"case {c:3d}: streams {ns:4d} blocks {nb:2d} snr {snr:5.1f} cuts {cuts} {'dev' if on_dev else 'host'} {'go' if go else 'py'} "
               f"records {len(want):5d} {'ok' if ok else 'MISMATCH'}", flush=True)
         if not ok:
             sw, sg = set(want), set(got)
