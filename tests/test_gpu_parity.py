@@ -389,6 +389,28 @@ def test_snr_sweep_matches_oracle_per_snr(dsp, protocol):
     assert all(recovered[s] == 0.0 for s in snrs if s <= 4), recovered
 
 
+def test_config2_literal_50ppm_rf_offset_is_parity_only(dsp, protocol):
+    """Config 2, second variant: a literal +-50 ppm of the 915 MHz carrier is
+    +-45.75 kHz, far outside what the matched filter passes.  The reference recovers none
+    of those packets; what is checked is that the CUDA path returns exactly the records
+    the oracle returns (false candidates included) and likewise validates none."""
+    from rtldavis_b200 import synth
+    n_blocks, per = 12, 4
+    caps = [synth.make_capture(5200 + s, n_blocks * 8192, per, 30.0, station=s % 8,
+                               df_hz=(45750.0 if s % 2 else -45750.0), clock_ppm=(50.0 if s % 2 else -50.0))
+            for s in range(8)]
+    iq = np.stack([c.iq for c in caps])
+    bd = dsp.BatchDemodulator(protocol.new_packet_config(14), 8, max_blocks=n_blocks)
+    bd.submit(iq)
+    got = _gpu_rows(bd.fetch())
+    bd.close()
+    want = _oracle_rows(iq)
+    assert got == want
+    sent = {(s, e.message) for s, c in enumerate(caps) for e in c.packets}
+    valid = {(r[0], bytes(protocol.swap_bit_order(b) for b in r[3][2:])) for r in got if r[4]}
+    assert len(sent) == 8 * per and not (sent & valid)
+
+
 # ---------------------------------------------------------------------------
 # complex input (dsp.py:144-151), the live pyrtlsdr entry
 # ---------------------------------------------------------------------------
