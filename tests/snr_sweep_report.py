@@ -4,7 +4,9 @@ AWGN 0..20 dB in 2 dB steps, residual carrier +-3 kHz, sample clock +-50 ppm, 40
 stream.  Per SNR: every record of the CUDA path (CRC-valid or not: stream, call, index, 10 bytes,
 verdict) against the C oracle on a host copy of the same bytes, the share of embedded packets that
 come back CRC-valid, and how many records needed a decision bit corrected by the fp64 re-check.
-Usage: python tests/snr_sweep_report.py [streams_per_snr=372] [blocks=328]"""
+Usage: python tests/snr_sweep_report.py [streams_per_snr=372] [blocks=328] [snr,snr,...]
+With an explicit SNR list the stream count is not topped up to 4 096 (config 2 at full size is
+`snr_sweep_report.py 1024 328 20`: bench.py's workload, every record against the oracle)."""
 import os
 import sys
 import time
@@ -27,16 +29,17 @@ def main():
     n_blocks = int(sys.argv[2]) if len(sys.argv) > 2 else 328
     n_packets, B = 40, 8192
     n_samples = n_blocks * B
-    snrs = list(range(0, 21, 2))
+    snrs = [int(x) for x in sys.argv[3].split(",")] if len(sys.argv) > 3 else list(range(0, 21, 2))
+    top_up = 0 if len(sys.argv) > 3 else max(0, 4096 - per * len(snrs))
     L = _lib.load()
     cfg = protocol.new_packet_config(14)
-    print(f"{len(snrs)} SNRs x {per} streams (+{4096 - per * len(snrs)} at the last) x {n_blocks} blocks of {B} samples, "
+    print(f"{len(snrs)} SNRs x {per} streams (+{top_up} at the last) x {n_blocks} blocks of {B} samples, "
           f"{n_packets} packets per stream")
     print(f"{'SNR dB':>6} {'streams':>7} {'records':>8} {'mismatch':>8} {'CRC-valid':>9} {'embedded':>8} "
           f"{'recovered':>9} {'fp64-fixed':>10} {'oracle s':>8}")
     tot_rec = tot_bad = tot_streams = 0
     for i, snr in enumerate(snrs):
-        ns = per + (4096 - per * len(snrs) if i == len(snrs) - 1 and per * len(snrs) <= 4096 else 0)
+        ns = per + (top_up if i == len(snrs) - 1 else 0)
         seed = 7000 + i
         buf = torch.empty((ns, 2 * n_samples), dtype=torch.uint8, device="cuda")
         _lib.check(L.davis_synth_fill(buf.data_ptr(), ns, 2 * n_samples, n_samples, seed, n_packets,
