@@ -54,6 +54,7 @@
 #include <algorithm>
 
 #include "davis_kernels.cuh"
+#include "davis_async.cuh"
 
 namespace davis {
 
@@ -118,33 +119,6 @@ __device__ __forceinline__ float2 fir9_pair(const float2 (&r)[39], int q, float 
     acc = fma2(f2(c2, c2), add2(r[q + 4], r[q + 8]), acc);
     acc = fma2(f2(c3, c3), add2(r[q + 5], r[q + 7]), acc);
     return acc;
-}
-
-// ---- bulk copy + mbarrier (sm_90+ PTX; the copy engine writes shared memory) ----
-__device__ __forceinline__ uint32_t smem_addr(const void *p) {
-    return (uint32_t)__cvta_generic_to_shared(p);
-}
-__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
-}
-__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes)
-                 : "memory");
-}
-__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void *src, uint32_t bytes, uint32_t bar) {
-    asm volatile(
-        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-        ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
-}
-__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
-    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-    uint32_t done;
-    do {
-        asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; "
-                     "selp.u32 %0, 1, 0, p; }" : "=r"(done) : "r"(bar), "r"(parity) : "memory");
-    } while (!done);
 }
 
 constexpr int DEMOD_THREADS = DEMOD_WARPS * 32;
