@@ -1,0 +1,46 @@
+"""Import the unmodified reference (``rtldavis.dsp`` / ``crc`` / ``protocol`` / ``worker``).
+
+TEST INFRASTRUCTURE: used by tests/, by ``bench.py``'s CPU legs and by ``oracle/gen_golden.py``
+only.  The modules come from ``oracle/_ref`` (byte-compiled from /root/reference by
+``oracle/stage_ref.py``; present on the GPU box) or, failing that, from /root/reference itself
+(build container).  ``available()`` is False when neither exists.
+"""
+from __future__ import annotations
+
+import importlib
+import os
+import sys
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+_REF_DIR = os.path.join(HERE, "_ref")
+_SRC_DIR = "/root/reference/src"
+
+
+def _root():
+    if os.path.exists(os.path.join(_REF_DIR, "rtldavis", "dsp.pyc")):
+        return _REF_DIR
+    if os.path.exists(os.path.join(_SRC_DIR, "rtldavis", "dsp.py")):
+        return _SRC_DIR
+    return None
+
+
+def available() -> bool:
+    return _root() is not None
+
+
+def kind() -> str:
+    """'ref' when the unmodified reference can be imported, else 'port'."""
+    return "ref" if available() else "port"
+
+
+def load():
+    """(dsp, crc, protocol) modules of the unmodified reference."""
+    root = _root()
+    if root is None:
+        raise ImportError("the reference is neither staged in oracle/_ref nor at /root/reference")
+    if root not in sys.path:
+        sys.path.insert(0, root)
+    dsp = importlib.import_module("rtldavis.dsp")
+    crc = importlib.import_module("rtldavis.crc")
+    protocol = importlib.import_module("rtldavis.protocol")
+    return dsp, crc, protocol

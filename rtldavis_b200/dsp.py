@@ -114,7 +114,9 @@ class BatchDemodulator:
             check(rc)
         self._keepalive = None
         self._last_blocks = 0
-        self.calls_done = 0
+        # blocks each stream has consumed since its last reset: the library numbers the calls
+        # of a stream from there (davis_hit.call), and reset(stream) restarts one stream only
+        self.calls_done = np.zeros(self.n_streams, dtype=np.int64)
 
     # -- lifetime ---------------------------------------------------------
     def close(self) -> None:
@@ -139,7 +141,9 @@ class BatchDemodulator:
         """Demodulator.reset (dsp.py:248-253) for one stream or all (-1)."""
         check(self._L.davis_reset(self._h, int(stream)), self._h)
         if stream < 0:
-            self.calls_done = 0
+            self.calls_done[:] = 0
+        else:
+            self.calls_done[int(stream)] = 0
 
     def submit(self, iq, cuda_stream: Optional[int] = None) -> None:
         B = self.cfg.block_size
@@ -181,6 +185,7 @@ class BatchDemodulator:
             self._keepalive = None
         check(rc, self._h)
         self._last_blocks = n_blocks
+        self.calls_done += n_blocks
 
     def _submit_complex(self, iq: np.ndarray, cuda_stream: Optional[int]) -> None:
         """Complex host input: complex64 stays complex64, everything else becomes
@@ -208,6 +213,7 @@ class BatchDemodulator:
             self._keepalive = None
         check(rc, self._h)
         self._last_blocks = n_blocks
+        self.calls_done += n_blocks
 
     def fetch(self, copy: bool = True) -> np.ndarray:
         """Packets of the submitted call.  With ``copy=False`` the array is a view of
@@ -216,9 +222,8 @@ class BatchDemodulator:
         ptr = C.c_void_p()
         rc = self._L.davis_fetch_hits_view(self._h, C.byref(ptr), C.byref(n))
         self._keepalive = None
-        check(rc, self._h)
-        self.calls_done += self._last_blocks
         self._last_blocks = 0
+        check(rc, self._h)
         if n.value == 0:
             return np.empty(0, dtype=HIT_DTYPE)
         buf = (C.c_char * (n.value * HIT_DTYPE.itemsize)).from_address(ptr.value)
@@ -231,13 +236,14 @@ class BatchDemodulator:
         return st
 
     def demodulate(self, iq) -> List[List[List[Packet]]]:
-        first_call = self.calls_done
+        first_call = self.calls_done.copy()
         self.submit(iq)
         n_blocks = self._last_blocks
         hits = self.fetch()
         out: List[List[List[Packet]]] = [[[] for _ in range(n_blocks)] for _ in range(self.n_streams)]
         for h in hits:
-            out[int(h["stream"])][int(h["call"]) - first_call].append(
+            s = int(h["stream"])
+            out[s][int(h["call"]) - int(first_call[s])].append(
                 Packet(int(h["index"]), h["data"].copy(), float(h["rssi"]), float(h["snr"])))
         return out
 

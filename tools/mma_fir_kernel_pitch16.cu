@@ -47,8 +47,8 @@
 // the SIMT kernel; tests/test_guard_band.py holds the numpy model of this arithmetic.
 #include <algorithm>
 
-#include "davis_async.cuh"
-#include "davis_kernels.cuh"
+#include "../rtldavis_b200/csrc/davis_async.cuh"
+#include "../rtldavis_b200/csrc/davis_kernels.cuh"
 
 namespace davis {
 namespace mma {

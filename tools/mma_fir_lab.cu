@@ -6,7 +6,7 @@
 //      variants and of their drain-only forms against the SIMT kernel.
 // Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -lineinfo -DDAVIS_MMA_LAB \
 //        -DDAVIS_MBAR_WATCHDOG -o tools/mma_fir_lab tools/mma_fir_lab.cu \
-//        rtldavis_b200/csrc/davis_demod.cu rtldavis_b200/csrc/davis_demod_mma.cu
+//        rtldavis_b200/csrc/davis_demod.cu tools/mma_fir_kernel_pitch64.cu
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -19,8 +19,7 @@ using namespace davis;
 
 namespace davis {
 void launch_demod_mma_lab(const View &vw, uint32_t *words, int n_streams, int tiles, int words_alloc,
-                          int limbs, int drain_only, float2 *z_dump, uint32_t a_lbo, uint32_t a_sbo,
-                          unsigned long long *prof, cudaStream_t st);
+                          int drain_only, float2 *z_dump, unsigned long long *prof, cudaStream_t st);
 }
 
 #define CK(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { printf("%s: %s\n", #x, cudaGetErrorString(e_)); exit(1); } } while (0)
@@ -95,19 +94,20 @@ static size_t diff_words(const std::vector<uint32_t> &a, const std::vector<uint3
     return dw;
 }
 
-static bool small_case(int limbs, uint32_t lbo, uint32_t sbo) {
-    Case c(3, 4);
-    const int n_sub = c.tiles * 4;
-    const size_t zn = (size_t)c.n_streams * n_sub * 7168;
+static bool small_case(int n_streams, int n_blocks) {
+    Case c(n_streams, n_blocks);
+    const int limbs = 3;
+    const size_t per_stream = (size_t)c.tiles * TILE_SAMPLES;
+    const size_t zn = (size_t)c.n_streams * per_stream;
     float2 *zd; uint32_t *w_ref, *w_mma;
     const size_t nw = (size_t)c.words_alloc * c.n_streams;
     CK(cudaMalloc(&zd, zn * sizeof(float2))); CK(cudaMemset(zd, 0, zn * sizeof(float2)));
     CK(cudaMalloc(&w_ref, nw * 4)); CK(cudaMalloc(&w_mma, nw * 4));
     CK(cudaMemset(w_ref, 0, nw * 4)); CK(cudaMemset(w_mma, 0, nw * 4));
     launch_demod(c.vw, w_ref, c.n_streams, c.tiles, c.words_alloc, nullptr, 0, 0);
-    launch_demod_mma_lab(c.vw, w_mma, c.n_streams, c.tiles, c.words_alloc, limbs, 0, zd, lbo, sbo, nullptr, 0);
+    launch_demod_mma_lab(c.vw, w_mma, c.n_streams, c.tiles, c.words_alloc, 0, zd, nullptr, 0);
     cudaError_t e = cudaDeviceSynchronize();
-    if (e != cudaSuccess) { printf("small case L=%d lbo=%u sbo=%u: %s\n", limbs, lbo, sbo, cudaGetErrorString(e)); exit(2); }
+    if (e != cudaSuccess) { printf("small case %d x %d: %s\n", n_streams, n_blocks, cudaGetErrorString(e)); exit(2); }
     std::vector<float2> z(zn);
     std::vector<uint8_t> V((size_t)2 * c.v_len + 64);
     std::vector<uint32_t> hr(nw), hm(nw);
@@ -120,7 +120,7 @@ static bool small_case(int limbs, uint32_t lbo, uint32_t sbo) {
         CK(cudaMemcpy(V.data() + c.carry_stride, c.input + s * c.input_stride, c.input_stride, cudaMemcpyDeviceToHost));
         for (int n = 0; n + 9 <= c.v_len; n++) {
             double zr, zi; host_z(V.data(), n, limbs == 3 ? T3 : T2, zr, zi);
-            const float2 got = z[(size_t)s * n_sub * 7168 + n + 8];
+            const float2 got = z[(size_t)s * per_stream + n + 8];
             const double scale = (limbs == 3 ? 8068069.0 : 31652.0) * 128.0;
             const double err = fmax(fabs(got.x - zr), fabs(got.y - zi)) / scale;
             if (err > worst) worst = err;
@@ -129,8 +129,8 @@ static bool small_case(int limbs, uint32_t lbo, uint32_t sbo) {
         }
     }
     size_t bits; const size_t dw = diff_words(hr, hm, c, &bits, 1);
-    printf("small case L=%d lbo=%u sbo=%u: z checked %zu, bad %zu, worst err %.3g of full scale; bitmap vs SIMT: %zu bits in %zu words differ\n",
-           limbs, lbo, sbo, checked, bad, worst, bits, dw);
+    printf("small case %d streams x %d blocks: z checked %zu, bad %zu, worst err %.3g of full scale; bitmap vs SIMT: %zu bits in %zu words differ\n",
+           n_streams, n_blocks, checked, bad, worst, bits, dw);
     cudaFree(zd); cudaFree(w_ref); cudaFree(w_mma);
     return bad == 0;
 }
@@ -139,13 +139,8 @@ int main(int argc, char **argv) {
     const int n_streams = argc > 1 ? atoi(argv[1]) : 1024;
     const int n_blocks = argc > 2 ? atoi(argv[2]) : 328;
     const int reps = argc > 3 ? atoi(argv[3]) : 5;
-    uint32_t lbo = 16, sbo = 128;
-    if (!small_case(3, 16, 128)) {
-        printf("trying the swapped stride roles\n");
-        if (!small_case(3, 128, 16)) { printf("neither descriptor reading gives the Hankel view\n"); return 3; }
-        lbo = 128; sbo = 16;
-    }
-    small_case(2, lbo, sbo);
+    // 3 x 4: one CTA per tile; 200 x 9: ranges that start inside streams (head decisions)
+    if (!small_case(3, 4) || !small_case(200, 9)) return 3;
 
     Case c(n_streams, n_blocks);
     const size_t nw = (size_t)c.words_alloc * c.n_streams;
@@ -157,15 +152,15 @@ int main(int argc, char **argv) {
     int clock_khz = 0;
     CK(cudaDeviceGetAttribute(&clock_khz, cudaDevAttrClockRate, 0));
     std::vector<uint32_t> ref(nw), got(nw);
-    const char *names[5] = {"SIMT k_demod (davis_demod.cu)", "mma 3 limbs", "mma 2 limbs", "mma 3 limbs, drain only", "mma 2 limbs, drain only"};
-    for (int v = 0; v < 5; v++) {
+    const char *names[3] = {"SIMT k_demod (davis_demod.cu)", "mma, 64-byte row pitch, 3 limbs", "mma, drain only"};
+    for (int v = 0; v < 3; v++) {
         uint32_t *out = words[v == 0 ? 0 : 1];
         CK(cudaMemset(out, 0, nw * 4));
         float best = 1e30f, sum = 0.f;
         for (int r = 0; r < reps + 1; r++) {
             CK(cudaEventRecord(e0));
             if (v == 0) launch_demod(c.vw, out, n_streams, c.tiles, c.words_alloc, nullptr, 0, 0);
-            else launch_demod_mma_lab(c.vw, out, n_streams, c.tiles, c.words_alloc, (v == 1 || v == 3) ? 3 : 2, v >= 3, nullptr, lbo, sbo, nullptr, 0);
+            else launch_demod_mma_lab(c.vw, out, n_streams, c.tiles, c.words_alloc, v == 2, nullptr, nullptr, 0);
             CK(cudaEventRecord(e1));
             CK(cudaEventSynchronize(e1));
             float ms; CK(cudaEventElapsedTime(&ms, e0, e1));
@@ -174,29 +169,29 @@ int main(int argc, char **argv) {
         CK(cudaGetLastError());
         size_t bits = 0, dw = 0;
         if (v == 0) CK(cudaMemcpy(ref.data(), out, nw * 4, cudaMemcpyDeviceToHost));
-        else if (v < 3) { CK(cudaMemcpy(got.data(), out, nw * 4, cudaMemcpyDeviceToHost)); dw = diff_words(ref, got, c, &bits, 1); }
+        else if (v < 2) { CK(cudaMemcpy(got.data(), out, nw * 4, cudaMemcpyDeviceToHost)); dw = diff_words(ref, got, c, &bits, 1); }
         printf("%-32s best %7.3f ms  mean %7.3f ms  %7.1f GB/s  %6.2f cyc/sample/lane@%d MHz  diff_bits=%zu (words %zu) of %.0f\n",
                names[v], best, sum / reps, 2.0 * samples / best * 1e-6,
                best * 1e-3 * clock_khz * 1e3 * 148 * 128 / samples, clock_khz / 1000, bits, dw, samples);
         fflush(stdout);
         if (v > 0) {
             // where the warps of the kernel spend their cycles (one extra, instrumented launch)
-            unsigned long long *prof; const size_t np = (size_t)148 * 20 * 6;
+            unsigned long long *prof; const size_t np = (size_t)148 * 21 * 8;
             CK(cudaMalloc(&prof, np * 8)); CK(cudaMemset(prof, 0, np * 8));
-            CK(cudaEventRecord(e0));
-            launch_demod_mma_lab(c.vw, out, n_streams, c.tiles, c.words_alloc, (v == 1 || v == 3) ? 3 : 2, v >= 3, nullptr, lbo, sbo, prof, 0);
-            CK(cudaEventRecord(e1)); CK(cudaEventSynchronize(e1));
-            float ms; CK(cudaEventElapsedTime(&ms, e0, e1));
+            launch_demod_mma_lab(c.vw, out, n_streams, c.tiles, c.words_alloc, v == 2, nullptr, prof, 0);
+            CK(cudaDeviceSynchronize());
             std::vector<unsigned long long> hp(np);
             CK(cudaMemcpy(hp.data(), prof, np * 8, cudaMemcpyDeviceToHost));
-            double epi[6] = {0}, ctl[6] = {0};
+            double epi[8] = {0}, fmt[8] = {0}, ctl[8] = {0};
             for (int b = 0; b < 148; b++)
-                for (int w = 0; w < 20; w++)
-                    for (int i = 0; i < 6; i++) (w < 16 ? epi : ctl)[i] += (double)hp[((size_t)b * 20 + w) * 6 + i];
-            const double mmas = samples / 1024.0;
-            printf("    instrumented %.3f ms; per MMA and warp, cycles: epilogue wait_full %.0f  ld %.0f  st %.0f  arrive %.0f | control wait_slot %.0f  wait_empty %.0f  wait_free %.0f\n",
-                   ms, epi[0] / (4 * mmas), epi[1] / (4 * mmas), epi[2] / (4 * mmas), epi[3] / (4 * mmas),
-                   ctl[0] / mmas, ctl[1] / mmas, ctl[2] / mmas);
+                for (int w = 0; w < 21; w++)
+                    for (int i = 0; i < 8; i++) (w < 16 ? epi : w < 20 ? fmt : ctl)[i] += (double)hp[((size_t)b * 21 + w) * 8 + i];
+            const double sets = samples / 4096.0;
+            printf("    cycles per set: epilogue warp: wait_full %.0f ld %.0f st %.0f arrive %.0f math %.0f barrier %.0f repack %.0f loop %.0f\n",
+                   epi[0] / (16 * sets), epi[1] / (16 * sets), epi[2] / (16 * sets), epi[3] / (16 * sets), epi[4] / (16 * sets), epi[5] / (16 * sets), epi[6] / (16 * sets), epi[7] / (16 * sets));
+            printf("                    formatter warp: wait_raw %.0f wait_a_free %.0f copy %.0f arrive %.0f loop %.0f | control: wait_a_ready %.0f wait_tm_empty %.0f issue %.0f wait_raw_free %.0f fetch %.0f loop %.0f\n",
+                   fmt[0] / (4 * sets), fmt[1] / (4 * sets), fmt[2] / (4 * sets), fmt[3] / (4 * sets), fmt[7] / (4 * sets),
+                   ctl[0] / sets, ctl[1] / sets, ctl[2] / sets, ctl[3] / sets, ctl[4] / sets, ctl[7] / sets);
             cudaFree(prof);
         }
     }

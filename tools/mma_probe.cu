@@ -110,6 +110,10 @@ int main() {
         run("kind::i8 TS (A in tensor memory)", n, R, 16, 128, 0, 2048, n * 16, 128, 0, ns, st, 2);
         run("kind::i8 SS M=64", n, R, 16, 128, 0, 2048, n * 16, 128, 0, ns, st, 5);
     }
+    for (int n : {192, 240, 256}) {
+        run("kind::i8 SS, A canonical no-swizzle, 3 k-steps same D", n, 63, 2048, 128, 0, 4096, n * 16, 128, 0, 1, 256);
+        run("kind::i8 SS, A canonical no-swizzle, 2 D stages", n, 64, 2048, 128, 0, 4096, n * 16, 128, 0, 2, 256);
+    }
     run("tcgen05.cp 128x256b Hankel source only", 48, R, 16, 128, 0, 2048, 48 * 16, 128, 0, 7, 64, 3);
     run("tcgen05.cp 128x256b Hankel + kind::i8 TS", 48, R, 16, 128, 0, 2048, 48 * 16, 128, 0, 7, 64, 4);
     run("tcgen05.cp 128x256b Hankel + kind::i8 TS", 32, R, 16, 128, 0, 2048, 32 * 16, 128, 0, 7, 64, 4);
