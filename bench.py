@@ -1,29 +1,35 @@
 #!/usr/bin/env python3
 """bench.py -- IQ Msample/s demodulated on B200, beside the reference's CPU path.
 
-One "step" = one pass of the whole hot path (demodulate -> sync search -> fp64
-confirm/slice/CRC -> carry) over one batch of synthetic captures.
+One "step" = one pass of the whole hot path (demodulate -> sync search -> confirm / slice /
+CRC -> carry) over one batch of synthetic captures.
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
-                    [--streams S] [--blocks NB] [--snr DB]
+                    [--streams S] [--blocks NB] [--snr DB] [--e2e-waves V]
 
-N = 1 workload: BASELINE.json configs[1] -- 1,024 independent 10 s captures
-(328 blocks of 8192 samples each), mixed station IDs, +-50 ppm clock error,
-+-3 kHz residual carrier.  N > 1 (torchrun): the same 1,024 streams on every
-rank, sharded by stream, no data-path collective ("weak" scaling).
+N = 1 workload: BASELINE.json configs[1] -- 1,024 independent 10 s captures (328 blocks of
+8192 samples each), mixed station IDs, +-50 ppm clock error, +-3 kHz residual carrier.
+N > 1 (torchrun): N x 1,024 streams sharded by stream through rtldavis_b200.shard, no
+data-path collective ("weak" scaling: 1,024 streams per GPU in the device-resident leg; in
+the end-to-end leg the same global batch is split in proportion to the host->device copy
+rate every GPU gets, probed at start-up).
 
-value   device-resident throughput (inputs already in HBM), CUDA-event timed
-e2e     same metric through BatchDemodulator.submit/fetch with PINNED HOST input:
-        H2D of every byte and D2H of the packet records inside the timed region
-roofline  the demodulation kernel alone, 2 algorithmic bytes per complex sample
-cpu_baseline  the reference algorithm on this box's host cores (oracle port)
+value        device-resident throughput (inputs already in HBM), CUDA-event timed
+e2e          the same metric through the public API with PINNED HOST input: H2D of every
+             byte and D2H of the packet records inside the timed region
+roofline     the demodulation kernel alone (frac) and the whole step (path_frac), 2 algorithmic
+             bytes per complex sample
+sustained    the device-resident loop again for >= 1.5 s with its own clock / power record
+parity_check records of the first 8 streams of every rank against the C oracle, gathered
+             with shard.gather_packets (outside the timed regions)
+cpu_baseline the reference's own CPU code (oracle/_ref: the unmodified rtldavis modules,
+             kind "ref") or, when that is not staged, the oracle's restatement (kind "port")
 """
 from __future__ import annotations
 
 import argparse
 import json
 import os
-import subprocess
 import sys
 import threading
 import time
@@ -36,6 +42,7 @@ sys.path.insert(0, ROOT)
 METRIC = "iq_msamples_per_s_demodulated"
 UNIT = "Msample/s"
 BLOCK = 8192
+SAMPLE_STREAMS, SAMPLE_BLOCKS = 8, 41          # the bounded sample the CPU legs are timed on
 
 
 def parse_args():
@@ -51,6 +58,12 @@ def parse_args():
     ap.add_argument("--seed", type=int, default=2024)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-sustained", action="store_true")
+    ap.add_argument("--uniform-e2e", action="store_true", help="end-to-end leg with the uniform split")
+    ap.add_argument("--e2e-waves", type=int, default=1,
+                    help="end-to-end: feed each GPU's streams in this many waves through a pinned ring of two "
+                         "wave buffers (BASELINE config 5: --streams 8192 --e2e-waves 8)")
+    ap.add_argument("--e2e-steps", type=int, default=0, help="steps of the end-to-end leg (default: --steps)")
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     return ap.parse_args()
 
@@ -61,42 +74,77 @@ def workload_name(a):
             f"stations 0-7, SNR {a.snr:g} dB, df +-3 kHz, clock +-50 ppm")
 
 
+def config_dict(a):
+    """Identical in both arms (the driver compares them)."""
+    return {"workload": workload_name(a), "streams_per_gpu": a.streams, "blocks_per_stream": a.blocks,
+            "block_size": BLOCK,
+            "l2": "inputs (%.2f GB per GPU) far exceed the 126 MB L2; no flush needed" % (a.streams * 2 * a.blocks * BLOCK / 1e9)}
+
+
 # ---------------------------------------------------------------------------
-# CPU baseline: the oracle's literal restatement of the reference, one process
-# per core, on a bounded sample of the same workload.
+# CPU legs: the reference's own Demodulator + CRC gate, one process per core, block by
+# block (worker.py:49-50), on a bounded sample of the workload.
 # ---------------------------------------------------------------------------
 def _cpu_worker(job):
-    iq, seconds, literal = job
-    from oracle import davis_oracle as O
-    o = O.CallOracle(O.OracleConfig(), literal_quantize=literal)
+    iq, seconds, use_ref = job
+    import logging
+    logging.disable(logging.CRITICAL)              # the parser logs every packet
     step = 2 * BLOCK
     n_blocks = iq.size // step
+    if use_ref:
+        from oracle import ref_loader
+        _, _, ref_protocol = ref_loader.load()
+        parser = ref_protocol.Parser(symbol_length=14)
+
+        def one(blk):
+            return len(parser.parse(parser.demodulator.demodulate(blk)))      # worker.py:49-50
+        reset = parser.demodulator.reset
+    else:
+        from oracle import davis_oracle as O
+        o = O.CallOracle(O.OracleConfig(), literal_quantize=True)
+
+        def one(blk):
+            return sum(p.crc_ok for p in o.demodulate(blk))
+        reset = o.reset
     done, packets = 0, 0
     t0 = time.perf_counter()
     while True:
         k = done % n_blocks
         if k == 0 and done:
-            o.reset()
-        packets += len(o.demodulate(iq[k * step:(k + 1) * step]))
+            reset()
+        packets += one(iq[k * step:(k + 1) * step])
         done += 1
         if time.perf_counter() - t0 >= seconds:
             break
     return done * BLOCK, time.perf_counter() - t0, packets
 
 
-def cpu_reference_rate(sample_iq: np.ndarray, seconds: float, cores: int, literal: bool = True):
+def cpu_kind():
+    from oracle import ref_loader
+    return ref_loader.kind()
+
+
+def cpu_reference_rate(sample_iq: np.ndarray, seconds: float, cores: int):
     """Aggregate Msample/s of `cores` processes each demodulating its own stream
     of the sample for ~`seconds` (block by block, as the reference is driven)."""
     import multiprocessing as mp
+    use_ref = cpu_kind() == "ref"
     ctx = mp.get_context("fork")
-    jobs = [(sample_iq[i % sample_iq.shape[0]], seconds, literal) for i in range(cores)]
+    jobs = [(sample_iq[i % sample_iq.shape[0]], seconds, use_ref) for i in range(cores)]
     t0 = time.perf_counter()
     with ctx.Pool(cores) as pool:
         res = pool.map(_cpu_worker, jobs)
     wall = time.perf_counter() - t0
     samples = sum(r[0] for r in res)
     busy = max(r[1] for r in res)
-    return samples / busy / 1e6, samples, wall
+    return samples / busy / 1e6, samples, wall, sum(r[2] for r in res)
+
+
+def cpu_sample_text(cores, seconds, kind):
+    what = ("the unmodified rtldavis Parser: demodulator.demodulate + parse (oracle/_ref)" if kind == "ref"
+            else "the oracle's literal restatement of dsp.Demodulator (per-sample quantize kept)")
+    return (f"first {SAMPLE_STREAMS} streams x {SAMPLE_BLOCKS} blocks of this workload (bytes of the GPU arm's own "
+            f"device generator, same seed); {cores} processes x ~{seconds:g} s, block by block through {what}")
 
 
 def c_port_rate(sample_iq: np.ndarray, cores: int):
@@ -116,13 +164,26 @@ def usable_cores() -> int:
         return os.cpu_count() or 1
 
 
+def device_sample(a, n_streams, n_blocks, local=0, seed=None):
+    """The first `n_streams` streams x `n_blocks` blocks of the bench workload as host bytes,
+    produced by the device generator the GPU arm uses (input generation only)."""
+    import torch
+    from rtldavis_b200 import _lib
+    L = _lib.load()
+    n_samples = a.blocks * BLOCK
+    buf = torch.empty((n_streams, 2 * n_samples), dtype=torch.uint8, device=f"cuda:{local}")
+    _lib.check(L.davis_synth_fill(buf.data_ptr(), n_streams, 2 * n_samples, n_samples,
+                                  a.seed if seed is None else seed, a.packets, a.snr, 3000.0, 50.0, local, None))
+    torch.cuda.synchronize(local)
+    return buf[:, : 2 * BLOCK * n_blocks].cpu().numpy()
+
+
 # ---------------------------------------------------------------------------
 # clocks
 # ---------------------------------------------------------------------------
 class ClockSampler:
     """Polls NVML (nvidia_ml_py) from a thread while the timed region runs: SM clock,
-    power and throttle reasons every ~0.5 ms (the timed region is tens of ms, too
-    short for `nvidia-smi -lms`)."""
+    power and throttle reasons every ~0.5 ms."""
     REASONS = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown",
                0x4: "sw_power_cap"}
 
@@ -182,6 +243,7 @@ class ClockSampler:
                 if r[2] & bit:
                     reasons.add(nm)
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": self.max_sm,
+                "sm_mhz_min": min(sm) if sm else None,
                 "power_w_max": max((r[1] for r in self.rows), default=None),
                 "samples": len(sm), "reasons": sorted(reasons)}
 
@@ -196,40 +258,41 @@ def measured_peak():
 
 
 # ---------------------------------------------------------------------------
-# reference arm: the reference's CPU algorithm (oracle port) on all host cores
+# reference arm: the reference's own CPU implementation on all host cores
 # ---------------------------------------------------------------------------
 def run_reference(a):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
-    from rtldavis_b200 import synth
     cores = usable_cores()
-    # bounded sample of the same workload: a handful of distinct streams (numpy
-    # generator, same signal model), each process loops over its stream
-    n_distinct = min(cores, 8)
-    sample_blocks = min(a.blocks, 41)
-    iq, _ = synth.make_batch(n_distinct, sample_blocks * BLOCK,
-                             max(1, a.packets * sample_blocks // 328), a.snr, seed0=a.seed,
-                             df_range_hz=3000.0, ppm_range=50.0)
+    kind = cpu_kind()
+    input_note = "device generator (davis_synth_fill), the GPU arm's seed; input generation only, not timed"
+    try:
+        iq = device_sample(a, SAMPLE_STREAMS, min(a.blocks, SAMPLE_BLOCKS))
+    except Exception as e:                      # no CUDA device: the numpy generator, same signal model
+        from rtldavis_b200 import synth
+        iq, _ = synth.make_batch(SAMPLE_STREAMS, min(a.blocks, SAMPLE_BLOCKS) * BLOCK,
+                                 max(1, a.packets * SAMPLE_BLOCKS // 328), a.snr, seed0=a.seed,
+                                 df_range_hz=3000.0, ppm_range=50.0)
+        input_note = f"numpy generator rtldavis_b200.synth (no CUDA device: {type(e).__name__})"
     per_step = max(1.0, min(a.cpu_seconds, 150.0 / max(1, a.steps + a.warmup)))  # whole run <= ~2.5 min
     rates = []
     for i in range(a.warmup + a.steps):
-        rate, samples, wall = cpu_reference_rate(iq, per_step, cores, literal=True)
+        rate, samples, wall, _ = cpu_reference_rate(iq, per_step, cores)
         if i >= a.warmup:
             rates.append((rate, samples, wall))
     value = float(np.mean([r[0] for r in rates]))
     samples = int(np.mean([r[1] for r in rates]))
-    sample_txt = (f"{cores} processes x ~{per_step:.1f} s each looping over a {sample_blocks}-block "
-                  f"capture of the workload, block by block (unmodified algorithm incl. per-sample quantize)")
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": a.gpus,
         "steps": a.steps, "warmup": a.warmup,
         "ms_per_step": float(np.mean([r[2] for r in rates])) * 1e3,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
         "data": "synthetic",
-        "config": {"workload": workload_name(a), "sample": sample_txt},
-        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port",
-                         "sample": sample_txt, "samples_per_step": samples},
+        "config": config_dict(a),
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": kind,
+                         "sample": cpu_sample_text(cores, per_step, kind), "samples_per_step": samples,
+                         "input": input_note},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -240,13 +303,17 @@ def run_reference(a):
 # ---------------------------------------------------------------------------
 # graft arm
 # ---------------------------------------------------------------------------
-def run_graft(a):
-    import ctypes as C
+def _rows(rec):
+    return [(int(r["stream"]), int(r["call"]), int(r["index"]), r["data"].tobytes(), bool(r["crc_ok"]))
+            for r in rec]
 
+
+def run_graft(a):
     import torch
     import torch.distributed as dist
 
-    from rtldavis_b200 import _lib, dsp, protocol
+    from rtldavis_b200 import _lib, protocol, shard
+    from rtldavis_b200._lib import HIT_DTYPE
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -262,29 +329,45 @@ def run_graft(a):
             dist.barrier()
         torch.cuda.synchronize()
 
+    def all_max(x):
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def all_sum(x):
+        t = torch.tensor([x], dtype=torch.int64, device="cuda")
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return int(t.item())
+
     L = _lib.load()
     n_samples = a.blocks * BLOCK
     row = 2 * n_samples
+    seed = a.seed + 7919 * rank                         # every rank generates its own streams
+
+    def synth_fill(buf, n, seed_):
+        _lib.check(L.davis_synth_fill(buf.data_ptr(), n, row, n_samples, seed_, a.packets,
+                                      a.snr, 3000.0, 50.0, local, None))
+        torch.cuda.synchronize()
+
     dev = torch.empty((a.streams, row), dtype=torch.uint8, device="cuda")
-    seed = a.seed + 7919 * rank                         # every rank gets its own streams
-    _lib.check(L.davis_synth_fill(dev.data_ptr(), a.streams, row, n_samples, seed, a.packets,
-                                  a.snr, 3000.0, 50.0, local, None))
-    torch.cuda.synchronize()
+    synth_fill(dev, a.streams, seed)
 
     cfg = protocol.new_packet_config(14)
-    bd = dsp.BatchDemodulator(cfg, a.streams, device=local, max_blocks=a.blocks)
-    # a non-default stream: the library takes a NULL stream argument as "use the handle's own"
+    n_global = a.streams * world
+    # The global batch goes through the sharding layer (uniform split: a.streams per rank).
+    # Two sharded handles alternate (each carries its own copy of the per-stream state): batch i
+    # is submitted before batch i-1 is fetched, so the device->host copy of one batch's packet
+    # records and the host bookkeeping overlap the next batch's kernels.  Every kernel of both
+    # handles runs on ONE stream, in order, so k_demod's event timer is that of a kernel running alone.
+    sds = (shard.ShardedDemodulator(cfg, n_global, max_blocks=a.blocks, device=local),
+           shard.ShardedDemodulator(cfg, n_global, max_blocks=a.blocks, device=local))
+    assert sds[0].count == a.streams
+    bds = (sds[0].local, sds[1].local)
     stream = torch.cuda.Stream(device=local)
     sptr = stream.cuda_stream
     assert sptr != 0
-
-    # Two handles alternate (each carries its own copy of the per-stream state): batch i is
-    # submitted before batch i-1 is fetched, so the device->host copy of one batch's packet
-    # records (the handle's own copy stream) and the host-side bookkeeping overlap the next
-    # batch's kernels.  Every kernel of both handles runs on ONE stream, in order, so the
-    # per-kernel event timers are those of kernels running alone.
-    bd_b = dsp.BatchDemodulator(cfg, a.streams, device=local, max_blocks=a.blocks)
-    bds = (bd, bd_b)
 
     def run_steps(n, collect, on_stream=sptr):
         pending, hits = None, None
@@ -317,95 +400,162 @@ def run_graft(a):
     barrier()
     clocks = sampler.stop()
     launches = launches[0]
-    ms_total = e0.elapsed_time(e1)
+    ms_step = all_max(e0.elapsed_time(e1)) / a.steps
+    n_valid = all_sum(int(hits["crc_ok"].sum()))
+    samples_step = a.streams * n_samples * world
+    value = samples_step / (ms_step * 1e-3) / 1e6
 
-    # Extra, not the headline: the same loop with each handle on its own stream, so the
-    # latency-bound finish kernels of one batch run beside the FP32-bound k_demod of the
-    # other.  Faster as a whole, but the per-kernel timers then measure kernels that share
-    # the GPU, so `value` and `roofline` above come from the single-stream run.
+    # ---- the same loop for >= 1.5 s: what clocks and power do under a sustained FP32-bound load ----
+    sustained = None
+    if not a.no_sustained:
+        s_steps = max(a.steps, int(np.ceil(1500.0 / ms_step)))
+        sampler2 = ClockSampler(local)
+        barrier()
+        sampler2.start()
+        s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s0.record(stream)
+        run_steps(s_steps, lambda st: None)
+        s1.record(stream)
+        barrier()
+        sc = sampler2.stop()
+        s_ms = all_max(s0.elapsed_time(s1)) / s_steps
+        sustained = {"steps": s_steps, "ms_per_step": s_ms, "value": samples_step / (s_ms * 1e-3) / 1e6,
+                     "unit": UNIT, "timed_region_s": s_ms * s_steps * 1e-3, "clocks": sc}
+
+    # Extra, not the headline: the same loop with each handle on its own stream, so the finish
+    # kernels of one batch run beside the FP32-bound k_demod of the other.
     run_steps(2, lambda st: None, on_stream=None)
     barrier()
     t0 = time.perf_counter()
     run_steps(a.steps, lambda st: None, on_stream=None)
     torch.cuda.synchronize()
-    dt2 = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device="cuda")
-    if world > 1:
-        dist.all_reduce(dt2, op=dist.ReduceOp.MAX)
-    two_streams_ms = float(dt2.item()) / a.steps * 1e3
-    t = torch.tensor([ms_total], dtype=torch.float64, device="cuda")
-    n_valid = torch.tensor([int(hits["crc_ok"].sum())], dtype=torch.int64, device="cuda")
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        dist.all_reduce(n_valid, op=dist.ReduceOp.SUM)   # host-side style gather of a count
-    ms_step = float(t.item()) / a.steps
-    samples_step = a.streams * n_samples * world
-    value = samples_step / (ms_step * 1e-3) / 1e6
+    two_streams_ms = all_max(time.perf_counter() - t0) / a.steps * 1e3
 
-    # ---- roofline of the demodulation kernel (CUDA events inside the library,
-    #      on the launching stream, around that kernel only) ----
+    # ---- roofline: the demodulation kernel (CUDA events inside the library, on the launching
+    #      stream, around that kernel only) and the whole step ----
     peak, peak_src = measured_peak()
     demod_avg = float(np.mean(demod_ms))
-    ach = 2.0 * a.streams * n_samples / (demod_avg * 1e-3) / 1e9
+    alg_bytes = 2 * a.streams * n_samples
+    ach = alg_bytes / (demod_avg * 1e-3) / 1e9
+    path_ach = alg_bytes / (ms_step * 1e-3) / 1e9
     roofline = {"bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
                 "traffic": None, "peak_source": peak_src, "kernel": "k_demod",
-                "kernel_ms": demod_avg, "search_ms": float(np.mean(search_ms)),
-                "finish_ms": float(np.mean(finish_ms)),
+                "limited_by": "FP32 issue rate (FMA pipe ~80 % busy, DRAM ~33 %): the HBM figure is the "
+                              "north_star's roofline, not this kernel's binding resource",
+                "kernel_ms": demod_avg,
+                "path_achieved": path_ach, "path_frac": path_ach / peak,
+                "behind_demod_ms": ms_step - demod_avg,
+                "chain_search_ms_sum": float(np.mean(search_ms)),
+                "chain_finish_ms_sum": float(np.mean(finish_ms)),
+                "chain_note": "sums over the two search/finish chains, which overlap each other behind "
+                              "k_demod; behind_demod_ms (ms_per_step - kernel_ms) is their critical path",
                 "frac_of_nominal_8TBs": ach / 8000.0,
-                "algorithmic_bytes_per_launch": 2 * a.streams * n_samples}
+                "algorithmic_bytes_per_launch": alg_bytes}
     prof = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(prof):
         try:
             with open(prof) as f:
                 cap = json.load(f)
             # the ncu capture is of the default workload; any other size has no capture
-            if cap.get("algorithmic_bytes_per_launch") == roofline["algorithmic_bytes_per_launch"]:
+            if cap.get("algorithmic_bytes_per_launch") == alg_bytes:
                 roofline["traffic"] = cap.get("k_demod_dram_bytes_per_launch")
         except Exception:
             pass
 
+    # ---- parity: the first 8 streams of every rank against the C oracle, gathered through
+    #      the sharding layer (fresh state, one batch; outside every timed region) ----
+    from oracle import c_oracle as CO
+    n_chk = min(8, a.streams)
+    sds[0].reset()
+    sds[0].submit(dev)
+    mine = sds[0].fetch()
+    got_all = shard.gather_packets(mine[mine["stream"] < n_chk], sds[0].first_stream)
+    rec = CO.batch_records(dev[:n_chk].cpu().numpy(), block=BLOCK)
+    orc = np.zeros(len(rec), dtype=HIT_DTYPE)
+    for k in ("stream", "call", "index", "data", "crc_ok"):
+        orc[k] = rec[k]
+    want_all = shard.gather_packets(orc, sds[0].first_stream)
+    parity = None
+    if rank == 0:
+        g_rows, w_rows = _rows(got_all), _rows(want_all)
+        parity = {"streams": n_chk * world, "records": len(w_rows),
+                  "mismatch": 0 if g_rows == w_rows else max(1, len(set(g_rows) ^ set(w_rows))),
+                  "crc_valid": sum(r[4] for r in w_rows),
+                  "how": "fresh state, one batch through shard.ShardedDemodulator; records of the first "
+                         f"{n_chk} streams of every rank gathered with shard.gather_packets and compared "
+                         "(stream, call, index, 10 bytes, CRC verdict, order) with oracle/davis_oracle.c"}
+
     # ---- end to end: pinned host input, H2D + records D2H inside the timed region ----
     e2e = None
     if not a.no_e2e:
-        host = torch.empty((a.streams, row), dtype=torch.uint8, pin_memory=True)
-        host.copy_(dev)
-        torch.cuda.synchronize()
-        host_np = host.numpy()
-        bd2 = dsp.BatchDemodulator(cfg, a.streams, device=local, max_blocks=a.blocks)
+        weights, probe = None, None
+        if world > 1 and not a.uniform_e2e:
+            probe = shard.probe_h2d_weights(local)
+            weights = probe
+        waves = max(1, a.e2e_waves)
+        e_steps = a.e2e_steps or a.steps
+        mine_n = shard.partition(n_global, world, weights)[rank][1]
+        per_wave = (mine_n + waves - 1) // waves
+        wave_n = [min(per_wave, mine_n - w * per_wave) for w in range(waves) if mine_n - w * per_wave > 0]
+        # pinned ring of (at most) two wave buffers, filled once from the device generator; a wave
+        # reads ring[w % 2] -- every byte of every wave crosses the host link in every step
+        ring = []
+        for w in range(min(2, len(wave_n))):
+            tmp = torch.empty((per_wave, row), dtype=torch.uint8, device="cuda")
+            synth_fill(tmp, per_wave, seed + 101 * (w + 1))
+            hbuf = torch.empty((per_wave, row), dtype=torch.uint8, pin_memory=True)
+            hbuf.copy_(tmp)
+            torch.cuda.synchronize()
+            ring.append(hbuf.numpy())
+            del tmp
+        from rtldavis_b200 import dsp
+        handles = [dsp.BatchDemodulator(cfg, n, device=local, max_blocks=a.blocks) for n in wave_n]
+
+        def e2e_step():
+            h2d = d2h = valid = 0
+            for w, (bd2, n) in enumerate(zip(handles, wave_n)):
+                bd2.submit(ring[w % 2][:n])
+                h2 = bd2.fetch(copy=False)
+                st2 = bd2.stats()
+                h2d += int(st2.h2d_bytes); d2h += int(st2.d2h_bytes); valid += int(h2["crc_ok"].sum())
+            return h2d, d2h, valid
+
         for _ in range(max(1, min(a.warmup, 2))):
-            bd2.submit(host_np)
-            h2 = bd2.fetch(copy=False)
+            e2e_step()
         barrier()
         t0 = time.perf_counter()
-        h2d = d2h = 0
-        for _ in range(a.steps):
-            bd2.submit(host_np)
-            h2 = bd2.fetch(copy=False)
-            st2 = bd2.stats()
-            h2d, d2h = int(st2.h2d_bytes), int(st2.d2h_bytes)
+        for _ in range(e_steps):
+            h2d, d2h, valid = e2e_step()
         torch.cuda.synchronize()
-        dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device="cuda")
+        mine_dt = time.perf_counter() - t0
+        dt = all_max(mine_dt)
+        e2e_samples = n_global * n_samples
+        e2e = {"value": e2e_samples * e_steps / dt / 1e6, "unit": UNIT,
+               "h2d_bytes_per_step": all_sum(h2d), "d2h_bytes_per_step": all_sum(d2h),
+               "ms_per_step": dt / e_steps * 1e3, "steps": e_steps,
+               "valid_packets_last_step": all_sum(valid),
+               "streams_this_rank": mine_n, "waves": len(wave_n),
+               "split": "uniform" if weights is None else "weighted by the probed host->device rate of every rank",
+               "h2d_probe_gbs": probe}
         if world > 1:
-            dist.all_reduce(dt, op=dist.ReduceOp.MAX)
-        e2e_val = samples_step * a.steps / float(dt.item()) / 1e6
-        e2e = {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": h2d * world,
-               "d2h_bytes_per_step": d2h * world,
-               "ms_per_step": float(dt.item()) / a.steps * 1e3,
-               "valid_packets_last_step": int(h2["crc_ok"].sum())}
-        bd2.close()
+            counts = [torch.zeros(1, dtype=torch.int64, device="cuda") for _ in range(world)]
+            dist.all_gather(counts, torch.tensor([mine_n], dtype=torch.int64, device="cuda"))
+            e2e["streams_per_rank"] = [int(c.item()) for c in counts]
+        for bd2 in handles:
+            bd2.close()
 
     # ---- CPU baseline on rank 0, N = 1 only ----
     cpu = None
     if rank == 0 and world == 1 and not a.no_cpu:
         cores = usable_cores()
-        n_distinct = min(cores, a.streams, 8)
-        sample_blocks = min(a.blocks, 41)
+        kind = cpu_kind()
+        n_distinct = min(a.streams, SAMPLE_STREAMS)
+        sample_blocks = min(a.blocks, SAMPLE_BLOCKS)
         sample = dev[:n_distinct, : 2 * BLOCK * sample_blocks].cpu().numpy()
-        rate, samples, wall = cpu_reference_rate(sample, a.cpu_seconds, cores, literal=True)
+        rate, samples, wall, _ = cpu_reference_rate(sample, a.cpu_seconds, cores)
         c_rate = c_port_rate(dev[: min(a.streams, 2 * cores), :].cpu().numpy(), cores)
-        cpu = {"value": rate, "unit": UNIT, "cores": cores, "kind": "port",
-               "sample": (f"first {n_distinct} streams x {sample_blocks} blocks of this workload; "
-                          f"{cores} processes x ~{a.cpu_seconds:g} s, block by block through the "
-                          f"oracle's literal restatement of dsp.Demodulator (per-sample quantize kept)"),
+        cpu = {"value": rate, "unit": UNIT, "cores": cores, "kind": kind,
+               "sample": cpu_sample_text(cores, a.cpu_seconds, kind),
                "samples_timed": samples, "wall_s": wall,
                "c_port_value": c_rate,
                "c_port_note": f"oracle/davis_oracle.c, {cores} threads, whole captures (not the reference's speed; a stronger CPU bar)"}
@@ -415,24 +565,26 @@ def run_graft(a):
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps,
             "warmup": a.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": workload_name(a), "streams_per_gpu": a.streams,
-                       "blocks_per_stream": a.blocks, "block_size": BLOCK,
-                       "l2": "inputs (%.2f GB per GPU) far exceed the 126 MB L2" % (a.streams * row / 1e9),
-                       "pipelining": "two handles alternate: batch i is submitted before batch i-1 is fetched "
-                                     "(its record copy overlaps the next batch's kernels); all kernels on one stream",
-                       "decision_arithmetic": "fp32 streaming kernel; every bit of every reported packet re-derived with an error bound (fp32 outside the guard band, fp64 inside), RSSI/SNR/discriminator mean in fp64"},
-            "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e,
+            "config": config_dict(a),
+            "notes": {"pipelining": "two sharded handles alternate: batch i is submitted before batch i-1 is fetched "
+                                    "(its record copy overlaps the next batch's kernels); k_demod of both runs on one "
+                                    "stream, the second search/finish chain and the record copies on the handles' own streams",
+                      "decision_arithmetic": "fp32 streaming kernel; every bit of every reported packet re-derived with an "
+                                             "error bound (fp32 outside the guard band, fp64 inside), RSSI/SNR/discriminator mean in fp64",
+                      "sharding": f"{n_global} streams over {world} rank(s) through rtldavis_b200.shard, no data-path collective"},
+            "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "sustained": sustained,
+            "parity_check": parity,
             "two_streams": {"value": samples_step / (two_streams_ms * 1e-3) / 1e6, "unit": UNIT,
                             "ms_per_step": two_streams_ms,
                             "note": "same loop, one stream per handle (kernels of consecutive batches overlap); "
                                     "host wall clock; not used for value/roofline"},
             "gpu_launches": int(launches), "clocks": clocks,
-            "valid_packets_per_step": int(n_valid.item()),
+            "valid_packets_per_step": n_valid,
             "embedded_packets_per_step": a.streams * a.packets * world,
         }
         emit(line)
-    bd.close()
-    bd_b.close()
+    for sd in sds:
+        sd.close()
     if world > 1:
         dist.destroy_process_group()
     return 0

@@ -32,7 +32,7 @@ extern "C" {
 #define DAVIS_API
 #endif
 
-#define DAVIS_ABI_VERSION 2
+#define DAVIS_ABI_VERSION 3
 
 enum {
     DAVIS_OK = 0,
@@ -58,7 +58,7 @@ typedef struct davis_cfg {
     uint32_t preamble;         /* sync pattern, first symbol in the MSB: 0xCB89     */
     int32_t block_size;        /* samples per block: 8192 (Python) or 512 (Go)      */
     int32_t max_blocks;        /* largest n_blocks a call will pass (>= 1)          */
-    int32_t max_hits;          /* capacity of the per-call packet buffer; 0 = auto  */
+    int32_t max_hits;          /* most packets one call may return (DAVIS_E_OVERFLOW beyond); 0 = no limit */
     int32_t host_slots;        /* pipeline depth for host-memory input; 0 = auto    */
     int32_t host_group;        /* streams per pipeline stage for host input; 0=auto */
     int32_t flavor;            /* DAVIS_FLAVOR_PYTHON (0) or DAVIS_FLAVOR_GO (1), ABI >= 2 */
@@ -114,7 +114,8 @@ typedef struct davis_stats {
     float host_submit_ms;     /* host time inside davis_demod_u8 (enqueue only)      */
     float host_wait_ms;       /* host time the fetch spent waiting for the device    */
     float host_copy_ms;       /* host time copying packet records back               */
-    float host_sort_ms;       /* host time ordering the records (dsp.py:175-186)     */
+    float host_sort_ms;       /* always 0: ordering (dsp.py:175-186) is done on the device */
+    uint64_t reruns;          /* chains run again with larger lists (sync-word-dense input) */
 } davis_stats;
 
 DAVIS_API int davis_abi_version(void);
@@ -158,7 +159,14 @@ DAVIS_API int davis_demod_c128(davis_handle *h, const double *iq, size_t samples
  * dsp.py:171-188, the index <= block_size filter and per-call dedupe of
  * dsp.py:190-205).  *n receives the number of packets; if it exceeds `cap` the
  * function returns DAVIS_E_OVERFLOW with *n set and nothing copied, and may be
- * called again with a larger buffer. */
+ * called again with a larger buffer.
+ * The device-side lists are sized for the sync-word matches of noise; an input that
+ * matches far more often (a transmitter repeating the sync word) makes the library run
+ * the affected chain again with larger lists (davis_stats.reruns) -- the reference
+ * answers such input (dsp.py:171-205), so does this.  The one remaining overflow error
+ * is a packet buffer the caller sized too small with davis_cfg.max_hits > 0: it is
+ * reported, never truncated, but the streams have advanced past the call by then
+ * (its packets are lost; davis_reset, or go on). */
 DAVIS_API int davis_fetch_hits(davis_handle *h, davis_hit *out, size_t cap, size_t *n);
 
 /* Same, without the copy: *out points at the handle's own (pinned) result buffer,

@@ -16,7 +16,13 @@ Per fixture:
               after every call, concatenated)
   disc_lo/hi, disc   a slice of the float64 ``discriminated`` stream
   truth_start / truth_msg   where the generator put packets (not reference output)
+
+The 10 s fixtures (``*_10s``) do not store the IQ (5.4 MB each): they store the generator's
+recipe (``synth.make_capture`` keyword arguments as JSON) and the SHA-256 of the bytes it must
+reproduce, next to the reference's rows and ``np.packbits(quantized)`` for the whole capture.
 """
+import hashlib
+import json
 import os
 import sys
 
@@ -81,8 +87,52 @@ def save(name, cap, block, disc_lo, disc_hi, as_complex=False):
           f"{len(cap.packets)} embedded")
 
 
+def save_seeded(name, block, n_samples, **recipe):
+    """A whole 10 s capture: recipe + hash instead of the IQ; every full block is fed."""
+    cap = synth.make_capture(n_samples=n_samples, **recipe)
+    n_blocks = n_samples // block
+    iq = cap.iq[: 2 * block * n_blocks]
+    rows, bits, _ = run_reference(iq, block)
+    np.savez_compressed(
+        os.path.join(OUT, name + ".npz"),
+        recipe=np.array(json.dumps(dict(recipe, n_samples=n_samples))),
+        sha256=np.array(hashlib.sha256(cap.iq.tobytes()).hexdigest()),
+        block=np.int64(block), n_blocks=np.int64(n_blocks),
+        pk_call=np.array([r[0] for r in rows], dtype=np.int64),
+        pk_index=np.array([r[1] for r in rows], dtype=np.int64),
+        pk_data=np.array([list(r[2]) for r in rows], dtype=np.uint8).reshape(-1, 10),
+        pk_crc=np.array([r[3] for r in rows], dtype=np.bool_),
+        pk_rssi=np.array([r[4] for r in rows], dtype=np.float64),
+        pk_snr=np.array([r[5] for r in rows], dtype=np.float64),
+        bits=np.packbits(bits), n_bits=np.int64(bits.size),
+        truth_start=np.array([p.start for p in cap.packets], dtype=np.int64),
+        truth_msg=np.array([list(p.message) for p in cap.packets], dtype=np.uint8).reshape(-1, 8),
+    )
+    print(f"{name}: {len(rows)} packets from the reference, {sum(r[3] for r in rows)} CRC-valid, "
+          f"{len(cap.packets)} embedded, {n_blocks} blocks")
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
+    if "--only-10s" not in sys.argv:
+        short_fixtures()
+    ten_second_fixtures()
+
+
+def ten_second_fixtures():
+    """What the short fixtures do not pin: BASELINE config 1 as it is
+    stated (10 s, 40 packets, station 0, high SNR), a 6 dB capture (marginal decisions, many
+    false candidates), a noise-only capture and config 2's literal +-50 ppm RF offset."""
+    B, n = 8192, 2_688_000                  # 10 s at 268.8 kS/s: 328 full blocks + a 1024-sample tail
+    save_seeded("config1_10s", B, n, seed=1001, n_packets=40, snr_db=30.0, station=0)
+    save_seeded("snr6_10s", B, n, seed=1002, n_packets=40, snr_db=6.0, station=3, df_hz=1500.0,
+                clock_ppm=-30.0)
+    save_seeded("noise_10s", B, n, seed=1003, n_packets=0, noise_only=True)
+    save_seeded("rf50ppm_10s", B, n, seed=1004, n_packets=40, snr_db=30.0, station=6,
+                df_hz=45750.0, clock_ppm=50.0)
+
+
+def short_fixtures():
     B = 8192
     # (1) high SNR; one burst placed so that its sync word starts within a few
     #     samples of a block boundary (duplicate reports in consecutive calls).

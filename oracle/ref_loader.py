@@ -8,6 +8,7 @@ only.  The modules come from ``oracle/_ref`` (byte-compiled from /root/reference
 from __future__ import annotations
 
 import importlib
+import importlib.machinery
 import os
 import sys
 
@@ -16,8 +17,15 @@ _REF_DIR = os.path.join(HERE, "_ref")
 _SRC_DIR = "/root/reference/src"
 
 
+def _ref_hook(path):
+    """Path hook for oracle/_ref only: byte-code modules with the suffix .rpyc."""
+    if not os.path.abspath(path).startswith(_REF_DIR) or not os.path.isdir(path):
+        raise ImportError
+    return importlib.machinery.FileFinder(path, (importlib.machinery.SourcelessFileLoader, [".rpyc"]))
+
+
 def _root():
-    if os.path.exists(os.path.join(_REF_DIR, "rtldavis", "dsp.pyc")):
+    if os.path.exists(os.path.join(_REF_DIR, "rtldavis", "dsp.rpyc")):
         return _REF_DIR
     if os.path.exists(os.path.join(_SRC_DIR, "rtldavis", "dsp.py")):
         return _SRC_DIR
@@ -38,6 +46,9 @@ def load():
     root = _root()
     if root is None:
         raise ImportError("the reference is neither staged in oracle/_ref nor at /root/reference")
+    if root == _REF_DIR and _ref_hook not in sys.path_hooks:
+        sys.path_hooks.insert(0, _ref_hook)
+        sys.path_importer_cache.pop(_REF_DIR, None)
     if root not in sys.path:
         sys.path.insert(0, root)
     dsp = importlib.import_module("rtldavis.dsp")

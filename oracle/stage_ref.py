@@ -3,7 +3,9 @@
 TEST INFRASTRUCTURE.  The reference is pure Python, so "compiling it from the sources
 where they lie" (/root/reference/src/rtldavis) means byte-compiling: every module the
 demodulation path and its production caller need is compiled with ``py_compile`` straight
-from the read-only tree into sourceless ``.pyc`` files under ``oracle/_ref/rtldavis/``.
+from the read-only tree into sourceless byte-code files under ``oracle/_ref/rtldavis/``
+(suffix ``.rpyc``: the gpurun snapshot leaves ``*.pyc`` behind; ``oracle/ref_loader.py``
+registers an importer for the suffix).
 No reference source is copied into the repository; ``oracle/_ref/`` is git-ignored (not
 gpurun-ignored), so the build output travels to the GPU box like the built ``.so`` files.
 
@@ -31,12 +33,12 @@ TOP = ["__init__", "version", "crc", "dsp", "protocol", "sensor_classes", "worke
 def stage(verbose: bool = False) -> bool:
     """True when oracle/_ref holds the byte-compiled reference afterwards."""
     if not os.path.isdir(REF_SRC):
-        return os.path.exists(os.path.join(OUT, "dsp.pyc"))
-    jobs = [(os.path.join(REF_SRC, m + ".py"), os.path.join(OUT, m + ".pyc")) for m in TOP]
+        return os.path.exists(os.path.join(OUT, "dsp.rpyc"))
+    jobs = [(os.path.join(REF_SRC, m + ".py"), os.path.join(OUT, m + ".rpyc")) for m in TOP]
     dec = os.path.join(REF_SRC, "decoders")
     for name in sorted(os.listdir(dec)):
         if name.endswith(".py") and not name.endswith("_test.py"):
-            jobs.append((os.path.join(dec, name), os.path.join(OUT, "decoders", name[:-3] + ".pyc")))
+            jobs.append((os.path.join(dec, name), os.path.join(OUT, "decoders", name[:-3] + ".rpyc")))
     for src, dst in jobs:
         os.makedirs(os.path.dirname(dst), exist_ok=True)
         # dfile: what tracebacks name; unchecked-hash pycs are valid without their source

@@ -30,7 +30,7 @@ class DavisStats(C.Structure):
                 ("search_ms", C.c_float), ("finish_ms", C.c_float), ("total_ms", C.c_float),
                 ("h2d_bytes", C.c_uint64), ("d2h_bytes", C.c_uint64),
                 ("host_submit_ms", C.c_float), ("host_wait_ms", C.c_float),
-                ("host_copy_ms", C.c_float), ("host_sort_ms", C.c_float)]
+                ("host_copy_ms", C.c_float), ("host_sort_ms", C.c_float), ("reruns", C.c_uint64)]
 
 
 HIT_DTYPE = np.dtype([("position", "<i8"), ("stream", "<u4"), ("call", "<u4"), ("index", "<i4"),
@@ -98,7 +98,7 @@ def load() -> C.CDLL:
         fn = getattr(L, name)
         if fn.restype is C.c_int or fn.restype is None:
             fn.restype = i32
-    if L.davis_abi_version() != 2:
+    if L.davis_abi_version() != 3:
         raise ImportError("libdavis_b200.so ABI version mismatch")
     _lib = L
     return L

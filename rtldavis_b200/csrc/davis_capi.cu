@@ -1,10 +1,10 @@
 // davis_capi.cu -- host side of libdavis_b200.so: the C ABI of include/davis_b200.h.
 //
-// Owns per-stream state (the carried tail of every stream and its call counter),
-// the pipeline stages used for host-memory input, and the host post-processing
-// that turns device records into the reference's per-call packet lists
-// (ordering of Demodulator._search, dsp.py:171-188; dedupe of _slice,
-// dsp.py:203-205).
+// Owns per-stream state (the carried tail of every stream and its call counter) and the
+// pipeline stages used for host-memory input.  Ordering (Demodulator._search,
+// dsp.py:171-188) and per-call dedupe (_slice, dsp.py:203-205) happen on the device; the host
+// only sizes the lists, and runs a group's chain again with larger ones when an input matches
+// the sync word more often than noise does (the reference never fails on such input).
 #include <algorithm>
 #include <chrono>
 #include <cstdio>
@@ -44,6 +44,10 @@ struct Group {
     int stage = 0, s0 = 0, ns = 0;
     size_t hit_off = 0;  unsigned int hit_cap = 0, n_hit = 0;
     uint32_t *planes = nullptr;          // bitmap rows of this group's streams
+    davis_hit *hits = nullptr;           // where the chain writes this group's packets
+    const uint8_t *dev_input = nullptr;  // first stream of the group on the device
+    size_t dev_stride = 0;
+    bool shared_demod = false;           // the bitmap came from a launch that covers several groups
     cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
 };
 
@@ -71,6 +75,9 @@ struct davis_handle {
 
     bool queued = false;
     int queued_blocks = 0;
+    // the queued call, kept for a second run of a group's chain (list overflow)
+    const uint8_t *q_iq = nullptr;  size_t q_bytes = 0, q_stride = 0;  bool q_on_device = false;
+    std::vector<davis_hit *> retry_hits;                    // larger packet buffers of re-run groups
     bool have_results = false;
     size_t n_results = 0;
     davis_hit *h_hits = nullptr;  size_t h_hits_cap = 0;       // pinned; the fetched packets
@@ -118,7 +125,7 @@ int grow(davis_handle *h, T **p, size_t *have, size_t want) {
 int tiles_needed(int v_len) { return (v_len + TILE_SAMPLES - 1) / TILE_SAMPLES; }
 
 int prepare_stage(davis_handle *h, Stage &st, int ns, int n_blocks, size_t staging_bytes,
-                  size_t rec_cap) {
+                  size_t rec_cap, size_t min_cand = 0, size_t min_conf = 0, size_t min_grp = 0) {
     const int v_len = h->n_carry + n_blocks * h->B;
     st.tiles = tiles_needed(v_len);
     st.words_alloc = st.tiles * TILE_WORDS + SEARCH_AHEAD;
@@ -129,17 +136,18 @@ int prepare_stage(davis_handle *h, Stage &st, int ns, int n_blocks, size_t stagi
     const double positions = (double)ns * ((double)n_blocks + h->W) * h->B;
     size_t want = (size_t)(positions * 17.0 / 65536.0 * 4.0) + 4096;
     size_t have = st.cand_cap;
-    if ((rc = grow(h, &st.cand, &have, want))) return rc;
-    st.cand_cap = (unsigned int)have;
+    if ((rc = grow(h, &st.cand, &have, std::max(want, min_cand)))) return rc;
+    st.cand_cap = (unsigned int)std::min<size_t>(have, 0xFFFFFFFFu);
     have = st.conf_cap;
-    if ((rc = grow(h, &st.conf, &have, want / 2))) return rc;
-    st.conf_cap = (unsigned int)have;
+    if ((rc = grow(h, &st.conf, &have, std::max(want / 2, min_conf)))) return rc;
+    st.conf_cap = (unsigned int)std::min<size_t>(have, 0xFFFFFFFFu);
     const int groups = (st.words_alloc + GROUP_WORDS - 1) / GROUP_WORDS;
     st.mark_words = (groups + 31) / 32;
     if ((rc = grow(h, &st.marks, &st.marks_cap, (size_t)ns * st.mark_words))) return rc;
     const int per_pos = (SPS * (PKT_SYMS - 1)) / GROUP_SAMPLES + 2;        // groups one position touches
     if ((rc = grow(h, &st.glist, &st.glist_cap,
-                   std::min((size_t)ns * groups, (size_t)st.conf_cap * per_pos)))) return rc;
+                   std::max(std::min((size_t)ns * groups, (size_t)st.conf_cap * per_pos),
+                            std::min((size_t)ns * groups, min_grp))))) return rc;
     if (!st.fixes) CU(cudaMalloc((void **)&st.fixes, sizeof(Fix) * FIX_CAP));
     if ((rc = grow(h, &st.recs, &st.recs_cap, rec_cap))) return rc;
     if ((rc = grow(h, &st.lost, &st.lost_cap, rec_cap))) return rc;
@@ -175,6 +183,8 @@ void release_groups(davis_handle *h) {
         for (auto &e : g.ev)
             if (e) { h->event_pool.push_back(e); e = nullptr; }
     h->groups.clear();
+    for (auto p : h->retry_hits) cudaFree(p);
+    h->retry_hits.clear();
 }
 
 // Enqueue every kernel of one group of streams on `st`.  `dev_input` points at the group's
@@ -182,9 +192,15 @@ void release_groups(davis_handle *h) {
 // written by a demodulation launch on another stream that covers several groups: this
 // chain then starts at the search and waits for that event first (its memsets do not).
 int run_group(davis_handle *h, Stage &stage, Group &g, int gi, const uint8_t *dev_input,
-              size_t input_stride, int n_blocks, cudaStream_t st, cudaEvent_t demod_done = nullptr) {
+              size_t input_stride, int n_blocks, cudaStream_t st, cudaEvent_t demod_done = nullptr,
+              int cur = -1) {
+    if (cur < 0) cur = h->cur;           // which carry buffer holds the state BEFORE this call
+    g.dev_input = dev_input;
+    g.dev_stride = input_stride;
+    g.shared_demod = demod_done != nullptr;
+    if (!g.hits) g.hits = h->d_hits + g.hit_off;
     View vw;
-    vw.carry = h->carry[h->cur] + (size_t)g.s0 * h->carry_stride + h->elem * (size_t)(h->n_keep - h->n_carry);
+    vw.carry = h->carry[cur] + (size_t)g.s0 * h->carry_stride + h->elem * (size_t)(h->n_keep - h->n_carry);
     vw.input = dev_input;
     vw.carry_stride = h->carry_stride;
     vw.input_stride = input_stride;
@@ -236,10 +252,9 @@ int run_group(davis_handle *h, Stage &stage, Group &g, int gi, const uint8_t *de
     unsigned int *count = stage.per_stream, *start = count + g.ns, *fill = start + g.ns + 1;
     CU(cudaMemsetAsync(count, 0, sizeof(unsigned int) * g.ns, st));
     launch_finalize(vw, sp, stage.recs, stage.lost, stage.tmp, count, stage.ctr, st);
-    launch_order(stage.tmp, stage.ctr, g.s0, g.ns, count, start, fill, stage.bucket,
-                 h->d_hits + g.hit_off, st);
-    launch_carry(h->carry[h->cur] + (size_t)g.s0 * h->carry_stride,
-                 h->carry[h->cur ^ 1] + (size_t)g.s0 * h->carry_stride, h->carry_stride, h->n_keep,
+    launch_order(stage.tmp, stage.ctr, g.s0, g.ns, count, start, fill, stage.bucket, g.hits, st);
+    launch_carry(h->carry[cur] + (size_t)g.s0 * h->carry_stride,
+                 h->carry[cur ^ 1] + (size_t)g.s0 * h->carry_stride, h->carry_stride, h->n_keep,
                  dev_input, input_stride, n_blocks * h->B, g.ns, h->d_blocks_done + g.s0, n_blocks,
                  h->elem, st);
     CU(cudaEventRecord(g.ev[3], st));
@@ -433,6 +448,7 @@ static int demod_common(davis_handle *h, const uint8_t *iq, size_t bytes_per_str
     h->have_results = false;
     h->stats = davis_stats{};
     h->stats.samples = (uint64_t)h->n_streams * n_blocks * h->B;
+    h->q_iq = iq; h->q_bytes = bytes_per_stream; h->q_stride = stream_stride; h->q_on_device = on_device;
 
     // split into groups
     int per_group = h->n_streams;
@@ -461,8 +477,9 @@ static int demod_common(davis_handle *h, const uint8_t *iq, size_t bytes_per_str
         g.planes = nullptr;
         g.s0 = gi * per_group;
         g.ns = std::min(per_group, h->n_streams - g.s0);
-        size_t cap = h->cfg.max_hits > 0 ? (size_t)h->cfg.max_hits
-                                         : 4096 + (size_t)g.ns * ((size_t)n_blocks + h->W) * 6;
+        // records BEFORE the per-call dedupe (a burst matches at up to ~14 adjacent sample phases);
+        // davis_cfg.max_hits bounds the packets handed to the caller, not this list
+        size_t cap = 4096 + (size_t)g.ns * ((size_t)n_blocks + h->W) * 6;
         g.hit_cap = (unsigned int)std::min<size_t>(cap, 0x7FFFFFFFu);
         g.hit_off = hit_total;
         hit_total += g.hit_cap;
@@ -518,14 +535,17 @@ static int demod_common(davis_handle *h, const uint8_t *iq, size_t bytes_per_str
             // whatever the caller enqueues next on its stream comes after every chain
             if (st != main_st) CU(cudaStreamWaitEvent(main_st, g.ev[4], 0));
         }
-    } else
+    } else {
+    // every stage is sized before the first kernel is enqueued: a failure here leaves the
+    // stream state untouched
+    const size_t stage_bytes = on_device ? 0 : (size_t)per_group * bytes_per_stream;
+    for (int si = 0; si < std::min(n_groups, (int)h->stages.size()); si++)
+        if ((rc = prepare_stage(h, h->stages[h->groups[si].stage], on_device ? h->n_streams : per_group,
+                                n_blocks, stage_bytes, h->groups[0].hit_cap)))
+            return rc;
     for (int gi = 0; gi < n_groups; gi++) {
         Group &g = h->groups[gi];
         Stage &stage = h->stages[g.stage];
-        const size_t stage_bytes = on_device ? 0 : (size_t)per_group * bytes_per_stream;
-        if ((rc = prepare_stage(h, stage, on_device ? h->n_streams : per_group, n_blocks, stage_bytes,
-                                g.hit_cap)))
-            return rc;
         cudaStream_t st = stage.st;
         const uint8_t *dev_in;
         size_t dev_stride;
@@ -541,6 +561,7 @@ static int demod_common(davis_handle *h, const uint8_t *iq, size_t bytes_per_str
             dev_stride = bytes_per_stream;
         }
         if ((rc = run_group(h, stage, g, gi, dev_in, dev_stride, n_blocks, st))) return rc;
+    }
     }
     h->cur ^= 1;
     for (auto &b : h->h_blocks_done) b += n_blocks;
@@ -569,6 +590,52 @@ int davis_demod_c128(davis_handle *h, const double *iq, size_t samples_per_strea
                         stream_stride_bytes, n_blocks, cuda_stream, 16);
 }
 
+// Second (third, ...) run of one group's chain after a list overflow, with every list that
+// overflowed resized from the device counters.  The stream state before the call is still in
+// the other carry buffer; the call counters are rewound for the group's streams first.
+static int rerun_group(davis_handle *h, int gi) {
+    Group &g = h->groups[gi];
+    Stage &stage = h->stages[g.stage];
+    const Counters c = h->h_ctr[gi];
+    const int n_blocks = h->queued_blocks;
+    h->stats.reruns += 1;
+    if (h->stats.reruns > 16 * (uint64_t)h->groups.size())
+        return fail(h, DAVIS_E_OVERFLOW, "device lists keep overflowing");
+    CU(cudaStreamSynchronize(stage.st));                    // later groups of this stage are done with its lists
+    const size_t min_cand = (c.overflow & 1u) ? (size_t)c.n_cand + c.n_cand / 4 + 1024 : 0;
+    const size_t min_conf = (c.overflow & 2u) ? (size_t)c.n_conf + c.n_conf / 4 + 1024 : 0;
+    const size_t min_grp = (c.overflow & 8u) ? (size_t)c.n_grp + c.n_grp / 4 + 1024 : 0;
+    size_t rec_cap = g.hit_cap;
+    if (c.overflow & 4u) {
+        rec_cap = std::min<size_t>((size_t)c.n_rec + c.n_rec / 4 + 1024, 0x7FFFFFFFu);
+        davis_hit *bigger = nullptr;
+        CU(cudaMalloc((void **)&bigger, rec_cap * sizeof(davis_hit)));
+        h->retry_hits.push_back(bigger);
+        g.hits = bigger;
+        g.hit_cap = (unsigned int)rec_cap;
+    }
+    // the lists of the stage may be shared with the bitmap of every stream (stage 0 of a
+    // shared demodulation launch): keep its row count
+    const int ns_alloc = (int)std::max<size_t>((size_t)g.ns, stage.planes_words / (size_t)std::max(stage.words_alloc, 1));
+    uint32_t *planes_before = stage.planes;
+    int rc = prepare_stage(h, stage, ns_alloc, n_blocks, stage.staging_bytes, rec_cap, min_cand, min_conf, min_grp);
+    if (rc) return rc;
+    if (stage.planes != planes_before) return fail(h, DAVIS_E_STATE, "bitmap moved during a re-run");
+    cudaStream_t st = stage.st;
+    launch_rewind(h->d_blocks_done + g.s0, g.ns, n_blocks, st);
+    const int cur_before = h->cur ^ 1;                      // demod_common flipped it after enqueueing
+    if (!h->q_on_device) {
+        // the staging buffer may hold a later group by now: bring this group's input again
+        CU(cudaMemcpy2DAsync(stage.staging, h->q_bytes, h->q_iq + (size_t)g.s0 * h->q_stride, h->q_stride,
+                             h->q_bytes, g.ns, cudaMemcpyHostToDevice, st));
+        h->stats.h2d_bytes += (uint64_t)h->q_bytes * g.ns;
+        g.planes = nullptr;
+        return run_group(h, stage, g, gi, stage.staging, h->q_bytes, n_blocks, st, nullptr, cur_before);
+    }
+    return run_group(h, stage, g, gi, g.dev_input, g.dev_stride, n_blocks, st,
+                     g.shared_demod ? h->demod_ev[1] : nullptr, cur_before);
+}
+
 // Wait for the queued call and bring its packets into the pinned result buffer.
 static int complete_call(davis_handle *h) {
     CU(cudaSetDevice(h->device));
@@ -590,16 +657,28 @@ static int complete_call(davis_handle *h) {
             h->stats.confirmed += c.n_conf;
             h->stats.records += c.n_rec;
             if (c.overflow) {
-                h->queued = false;
-                char msg[160];
-                snprintf(msg, sizeof msg,
-                         "device buffer overflow (mask %u): cand %u conf %u records %u; raise max_hits",
-                         c.overflow, c.n_cand, c.n_conf, c.n_rec);
-                return fail(h, DAVIS_E_OVERFLOW, msg);
+                // An input that matches the sync word far more often than noise does (a
+                // transmitter repeating it, a test pattern) overflows lists sized for noise.  The
+                // reference answers such input (dsp.py:171-205), so the group's chain runs again
+                // with lists sized from the counters, which hold the true counts.
+                const int rc_r = rerun_group(h, (int)gi);
+                if (rc_r) { h->queued = false; return rc_r; }
+                gi--;                               // look at the same group again
+                continue;
             }
             g.n_hit = c.n_hit;
             h->n_results += c.n_hit;
             h->stats.d2h_bytes += sizeof(Counters);
+        }
+        if (h->cfg.max_hits > 0 && h->n_results > (size_t)h->cfg.max_hits) {
+            // the one overflow that stays an error: a packet buffer the CALLER sized
+            h->queued = false;
+            char msg[200];
+            snprintf(msg, sizeof msg,
+                     "%zu packets exceed max_hits = %d; the streams have advanced past this call: "
+                     "raise max_hits and davis_reset, or go on without its packets",
+                     h->n_results, h->cfg.max_hits);
+            return fail(h, DAVIS_E_OVERFLOW, msg);
         }
         if (h->demod_ev[0]) {
             float ms;
@@ -636,7 +715,7 @@ static int complete_call(davis_handle *h) {
         size_t at = 0;
         for (const Group &g : h->groups) {
             if (!g.n_hit) continue;
-            CU(cudaMemcpyAsync(h->h_hits + at, h->d_hits + g.hit_off, sizeof(davis_hit) * g.n_hit,
+            CU(cudaMemcpyAsync(h->h_hits + at, g.hits, sizeof(davis_hit) * g.n_hit,
                                cudaMemcpyDeviceToHost, h->stages[g.stage].st));
             at += g.n_hit;
         }

@@ -87,6 +87,7 @@ void launch_order(const davis_hit *tmp, const Counters *ctr, int stream0, int n_
 void launch_carry(const uint8_t *carry_old, uint8_t *carry_new, size_t carry_stride, int keep,
                   const uint8_t *input, size_t input_stride, int n_new, int n_streams,
                   int64_t *blocks_done, int n_blocks, int elem, cudaStream_t st);
+void launch_rewind(int64_t *blocks_done, int n_streams, int n_blocks, cudaStream_t st);
 void launch_exact_disc(const View &vw, int stream, int v0, int n, double *out, cudaStream_t st);
 void launch_crc16(const uint8_t *data, size_t n, size_t len, uint16_t init, uint16_t poly,
                   int swap_bits, uint16_t *out, cudaStream_t st);

@@ -1270,6 +1270,15 @@ void launch_carry(const uint8_t *carry_old, uint8_t *carry_new, size_t carry_str
     }
 }
 
+// undo the call counter advance of k_carry for a group whose chain is run again with larger lists
+__global__ void k_rewind(int64_t *blocks_done, int n_streams, int n_blocks) {
+    const int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s < n_streams) blocks_done[s] -= n_blocks;
+}
+void launch_rewind(int64_t *blocks_done, int n_streams, int n_blocks, cudaStream_t st) {
+    k_rewind<<<(n_streams + 255) / 256, 256, 0, st>>>(blocks_done, n_streams, n_blocks);
+}
+
 // ---------------------------------------------------------------------------
 // debug / parity taps
 // ---------------------------------------------------------------------------

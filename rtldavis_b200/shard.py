@@ -9,25 +9,75 @@ records, a few hundred bytes per stream, done here with ``torch.distributed``
 from __future__ import annotations
 
 import os
-from typing import List, Optional, Tuple
+from typing import List, Optional, Sequence, Tuple
 
 import numpy as np
 
 from ._lib import HIT_DTYPE
 
 
-def partition(n_streams: int, world: int) -> List[Tuple[int, int]]:
-    """Contiguous ``(first_stream, count)`` per rank; the first ``n % world`` ranks
-    get one stream more.  Ranks beyond the stream count get ``(n_streams, 0)``."""
+def partition(n_streams: int, world: int, weights: Optional[Sequence[float]] = None
+              ) -> List[Tuple[int, int]]:
+    """Contiguous ``(first_stream, count)`` per rank.
+
+    Without ``weights`` the split is uniform: the first ``n % world`` ranks get one stream
+    more, ranks beyond the stream count get ``(n_streams, 0)``.  With ``weights`` (one
+    positive number per rank, e.g. the host->device copy rate each GPU gets while all of them
+    copy, ``probe_h2d_weights``) rank r gets ``n * w_r / sum(w)`` streams, rounded by largest
+    remainder: the end-to-end step ends with the slowest rank, and on a box whose GPUs hang
+    off unequal host links a uniform split leaves the faster links idle."""
     if n_streams < 0 or world < 1:
         raise ValueError("n_streams >= 0 and world >= 1 required")
-    base, extra = divmod(n_streams, world)
+    if weights is None:
+        base, extra = divmod(n_streams, world)
+        counts = [base + (1 if r < extra else 0) for r in range(world)]
+    else:
+        w = [float(x) for x in weights]
+        if len(w) != world or any(not (x > 0.0) for x in w):
+            raise ValueError("weights: one positive number per rank")
+        total = sum(w)
+        exact = [n_streams * x / total for x in w]
+        counts = [int(e) for e in exact]
+        left = n_streams - sum(counts)
+        order = sorted(range(world), key=lambda r: (counts[r] - exact[r], r))
+        for r in order[:left]:
+            counts[r] += 1
     out, at = [], 0
-    for r in range(world):
-        cnt = base + (1 if r < extra else 0)
+    for cnt in counts:
         out.append((at, cnt))
         at += cnt
     return out
+
+
+def probe_h2d_weights(device: int, seconds: float = 0.5, nbytes: int = 256 << 20) -> List[float]:
+    """Pinned host -> device GB/s of every rank while ALL ranks copy at once (the situation of
+    the end-to-end path), gathered on every rank: the ``weights`` of ``partition``.  Needs an
+    initialised process group whose backend can all_gather CUDA tensors; one rank: ``[rate]``."""
+    import time
+
+    import torch
+    import torch.distributed as dist
+
+    multi = dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1
+    h = torch.empty(nbytes, dtype=torch.uint8, pin_memory=True)
+    d = torch.empty(nbytes, dtype=torch.uint8, device=f"cuda:{device}")
+    d.copy_(h, non_blocking=True)
+    torch.cuda.synchronize(device)
+    if multi:
+        dist.barrier()
+    t0 = time.perf_counter()
+    n = 0
+    while time.perf_counter() - t0 < seconds:
+        d.copy_(h, non_blocking=True)
+        torch.cuda.synchronize(device)
+        n += 1
+    rate = n * nbytes / (time.perf_counter() - t0) / 1e9
+    if not multi:
+        return [rate]
+    mine = torch.tensor([rate], dtype=torch.float64, device=f"cuda:{device}")
+    every = [torch.zeros_like(mine) for _ in range(dist.get_world_size())]
+    dist.all_gather(every, mine)
+    return [float(x.item()) for x in every]
 
 
 def rank_world() -> Tuple[int, int, int]:
@@ -74,11 +124,12 @@ class ShardedDemodulator:
     (``uint8[count, n_blocks*2*block_size]``); ``fetch_gathered`` returns the whole
     batch's packets on rank 0."""
 
-    def __init__(self, cfg, n_streams: int, max_blocks: int = 1, device: Optional[int] = None, **kw):
+    def __init__(self, cfg, n_streams: int, max_blocks: int = 1, device: Optional[int] = None,
+                 weights: Optional[Sequence[float]] = None, **kw):
         from . import dsp
         rank, world, local = rank_world()
         self.rank, self.world = rank, world
-        self.first_stream, self.count = partition(n_streams, world)[rank]
+        self.first_stream, self.count = partition(n_streams, world, weights)[rank]
         self.n_streams = n_streams
         self.local = None
         if self.count:

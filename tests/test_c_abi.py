@@ -32,7 +32,7 @@ def test_library_loads_and_exports_every_declared_symbol():
     missing = [n for n in _declared() if not hasattr(L, n)]
     assert not missing, f"declared in include/davis_b200.h but not exported: {missing}"
     L.davis_abi_version.restype = C.c_int
-    assert L.davis_abi_version() == 2          # davis_cfg.flavor was added in version 2
+    assert L.davis_abi_version() == 3          # 2: davis_cfg.flavor; 3: davis_stats.reruns
     L.davis_strerror.restype = C.c_char_p
     assert L.davis_strerror(0) is not None
 

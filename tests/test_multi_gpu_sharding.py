@@ -27,6 +27,24 @@ def test_partition_covers_everything_once():
         shard.partition(4, 0)
 
 
+def test_weighted_partition_follows_the_link_rates():
+    """The 8-GPU box of profiles/r01_h2d_ceiling_8gpu.txt: 23.3 GB/s to GPUs 0-3, 36.0 to 4-7."""
+    w = [23.3] * 4 + [36.0] * 4
+    parts = shard.partition(8192, 8, weights=w)
+    counts = [c for _, c in parts]
+    assert sum(counts) == 8192 and [f for f, _ in parts] == [sum(counts[:r]) for r in range(8)]
+    assert counts[0] == counts[3] and counts[4] == counts[7]
+    assert abs(counts[4] / counts[0] - 36.0 / 23.3) < 0.01
+    # the slowest rank's time (streams / rate) drops from 1024 / 23.3 to the balanced figure
+    assert max(c / r for c, r in zip(counts, w)) < 0.80 * (1024 / 23.3)
+    assert shard.partition(7, 3, weights=[1, 1, 1]) == shard.partition(7, 3)
+    assert [c for _, c in shard.partition(5, 2, weights=[1e-9, 1.0])] == [0, 5]
+    with pytest.raises(ValueError):
+        shard.partition(8, 2, weights=[1.0])
+    with pytest.raises(ValueError):
+        shard.partition(8, 2, weights=[1.0, 0.0])
+
+
 def test_gather_is_identity_without_a_process_group():
     h = np.zeros(3, dtype=HIT_DTYPE)
     h["stream"] = [0, 1, 1]

@@ -7,7 +7,7 @@ test vectors, cited per test.
 import numpy as np
 import pytest
 
-from conftest import golden_rows, load_golden
+from conftest import TEN_SECOND_FIXTURES, golden_rows, load_golden, load_seeded
 from oracle import c_oracle as CO
 from oracle import davis_oracle as O
 
@@ -131,6 +131,42 @@ def test_c_oracle_matches_reference(name):
     assert np.all(np.abs(disc[lo:hi] - ref) <= 1e-12 * np.maximum(np.abs(ref), 1.0))
     got = CO.batch_packets(g["iq"], block=int(g["block"]))[0]
     assert [(p.call, p.index, p.data, p.crc_ok) for p in got] == golden_rows(g)
+
+
+# ---- whole 10 s captures: BASELINE config 1 as stated, 6 dB, noise only, +-45.75 kHz ----
+@pytest.mark.parametrize("name", TEN_SECOND_FIXTURES)
+def test_oracles_match_reference_on_10s_captures(name):
+    """328 blocks through the reference (oracle/gen_golden.py): every packet row, RSSI/SNR and
+    all 2 686 976 quantized bits, against the numpy call-by-call restatement, the numpy stream
+    formulation and the C restatement."""
+    g, iq = load_seeded(name)
+    cfg = _cfg(g)
+    B = cfg.block_size
+    want_rows = golden_rows(g)
+    want_bits = np.unpackbits(g["bits"])[: int(g["n_bits"])]
+    o = O.CallOracle(cfg)
+    got = []
+    for k in range(iq.size // (2 * B)):
+        got.extend(o.demodulate(iq[2 * B * k:2 * B * (k + 1)]))
+    assert [(p.call, p.index, p.data, p.crc_ok) for p in got] == want_rows
+    np.testing.assert_allclose([p.rssi for p in got], g["pk_rssi"], rtol=0, atol=1e-9)
+    np.testing.assert_allclose([p.snr for p in got], g["pk_snr"], rtol=0, atol=1e-9)
+    assert (O.stream_bits(iq) == want_bits).all()
+    assert (CO.stream_bits(iq) == want_bits).all()
+    got_c = CO.batch_packets(iq, block=B)[0]
+    assert [(p.call, p.index, p.data, p.crc_ok) for p in got_c] == want_rows
+
+
+def test_config1_fixture_is_what_baseline_states():
+    """BASELINE configs[0]: 10 s, station 0, 40 embedded packets, all recovered."""
+    g = load_golden("config1_10s")
+    rows = golden_rows(g)
+    assert int(g["n_blocks"]) == 328 and g["truth_msg"].shape[0] == 40
+    valid = {O.crc_gate(r[2])[0][2:] for r in rows if r[3]}
+    assert {bytes(m.tolist()) for m in g["truth_msg"]} == valid
+    assert all(m[0] & 7 == 0 for m in g["truth_msg"])
+    assert not any(r[3] for r in golden_rows(load_golden("noise_10s")))
+    assert not any(r[3] for r in golden_rows(load_golden("rf50ppm_10s")))
 
 
 def test_embedded_packets_are_recovered_at_high_snr():
