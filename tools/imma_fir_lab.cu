@@ -1,0 +1,221 @@
+// imma_fir_lab.cu -- compute-only model of a demodulation kernel whose 9-tap filter runs on the
+// legacy warp-level tensor path (mma.sync m16n8k32 u8 x s8 -> s32, SASS IMMA.16832.U8.S8): what does
+// a sample cost in issue cycles when the bytes come from shared memory (no global traffic)?
+// (development tool; the arithmetic is checked against the float64 evaluation on the host)
+// Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -o tools/imma_fir_lab tools/imma_fir_lab.cu
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstdint>
+#include <vector>
+#include <cuda_runtime.h>
+#define CK(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { printf("%s: %s\n", #x, cudaGetErrorString(e_)); exit(1); } } while (0)
+
+constexpr uint32_t MAGIC = 0x4B400000u;
+template <int L> __host__ __device__ constexpr int tap5(int i) {
+    return L == 3 ? (i == 0 ? 623995 : i == 1 ? 1699934 : i == 2 ? 4320285 : i == 3 ? 6966413 : 8068069)
+                  : (i == 0 ? 2448 : i == 1 ? 6669 : i == 2 ? 16949 : i == 3 ? 27330 : 31652);
+}
+__host__ __device__ constexpr int balanced_digit(long long v, int l) {
+    int d = 0;
+    for (int i = 0; i <= l; i++) { d = (int)(((v % 256) + 256 + 128) % 256) - 128; v = (v - d) / 256; }
+    return d;
+}
+template <int L> __host__ __device__ constexpr int kappa() {
+    const long long s = 2LL * tap5<L>(0) - 2LL * tap5<L>(2) + tap5<L>(4);
+    const long long w = L == 3 ? 65793 : 257;
+    return (int)(((s * 1274 + 5) / 10 + w / 2) / w);
+}
+template <int L> __host__ __device__ constexpr int byte_tap(int o, int comp, int l) {
+    if (o < 0 || o >= 18) return 0;
+    const int m = o >> 1, q = o & 1, ph = m & 3;
+    const bool uses_q = comp == 0 ? (ph & 1) : !(ph & 1);
+    if ((q == 1) != uses_q) return 0;
+    const int sign = comp == 0 ? ((ph == 0 || ph == 3) ? 1 : -1) : ((ph == 0 || ph == 1) ? 1 : -1);
+    return sign * balanced_digit(tap5<L>(m < 5 ? m : 8 - m), l);
+}
+template <int L> __device__ __forceinline__ float combine(float f0, float f1, float f2) {
+    if constexpr (L == 3) return f0 + fmaf(f1, 256.f, fmaf(f2, 65536.f, -65793.f * 12582912.f));
+    else return f0 + fmaf(f1, 256.f, -257.f * 12582912.f);
+}
+__device__ __forceinline__ void imma(int (&d)[4], const uint32_t (&a)[4], const uint32_t (&b)[2], const int (&c)[4]) {
+    asm("mma.sync.aligned.m16n8k32.row.col.s32.u8.s8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%10,%11,%12,%13};"
+        : "=r"(d[0]), "=r"(d[1]), "=r"(d[2]), "=r"(d[3])
+        : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b[0]), "r"(b[1]), "r"(c[0]), "r"(c[1]), "r"(c[2]), "r"(c[3]));
+}
+
+constexpr int WARPS = 24, SPAN = 1792, TILES = SPAN / 128;      // per warp: 14 warp tiles of 16 rows x 8 samples
+constexpr int BUF = 2 * WARPS * SPAN + 64;
+constexpr int OFF = 2;                                          // z[0] starts at sample OFF of the buffer
+
+// z[n] (n = 0 .. WARPS*SPAN-1, relative to byte 0 of the buffer) and the decision of (z[n], z[n+1]):
+// bit d of the span's 1792-bit string.  words_out: 64 words of 28 bits per warp and repetition.
+template <int L, bool DUMP>
+__global__ void __launch_bounds__(WARPS * 32, 1)
+k_lab(const uint8_t *__restrict__ src, uint32_t *__restrict__ words_out, float2 *__restrict__ z_out, int reps,
+      unsigned long long *cycles) {
+    extern __shared__ __align__(16) uint8_t buf[];
+    __shared__ uint32_t ballots[WARPS][TILES][4];
+    __shared__ float2 zx[WARPS + 1];
+    for (int i = threadIdx.x; i < BUF / 4; i += blockDim.x)
+        reinterpret_cast<uint32_t *>(buf)[i] = reinterpret_cast<const uint32_t *>(src)[i];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+    // B fragments: N tile j = 2 limb + comp, column n = g = sample offset; logical k = 4t+i <-> window byte
+    // 8t+i, k = 16+4t+i <-> byte 8t+4+i
+    uint32_t b[2 * L][2];
+#pragma unroll
+    for (int j = 0; j < 2 * L; j++)
+#pragma unroll
+        for (int h = 0; h < 2; h++) {
+            uint32_t w = 0;
+#pragma unroll
+            for (int i = 0; i < 4; i++)
+                w |= (uint32_t)(uint8_t)(int8_t)byte_tap<L>(8 * t + 4 * h + i - 2 * g, j & 1, j >> 1) << (8 * i);
+            b[j][h] = w;
+        }
+    // the accumulator bias as four registers that stay put (opaque to the compiler)
+    int cb[4];
+#pragma unroll
+    for (int e = 0; e < 4; e++) asm volatile("mov.b32 %0, %1;" : "=r"(cb[e]) : "r"((int)(MAGIC - (uint32_t)kappa<L>())));
+    __syncthreads();
+    const unsigned long long t0 = clock64();
+    uint32_t sink = 0;
+    for (int r = 0; r < reps; r++) {
+        const uint8_t *base = buf + 4 + 2 * SPAN * warp + 16 * g + 8 * t;   // row g of warp tile 0, thread's 8 bytes (4-byte aligned only, as in the kernel)
+        float2 carry_z = make_float2(0.f, 0.f);                              // z[7] of row 15 of the previous tile
+#pragma unroll 2
+        for (int k = 0; k < TILES; k++) {
+            const uint8_t *p = base + 256 * k;
+            uint32_t a[4];
+            a[0] = *reinterpret_cast<const uint32_t *>(p);
+            a[2] = *reinterpret_cast<const uint32_t *>(p + 4);
+            a[1] = *reinterpret_cast<const uint32_t *>(p + 128);
+            a[3] = *reinterpret_cast<const uint32_t *>(p + 132);
+            int d[2 * L][4];
+#pragma unroll
+            for (int j = 0; j < 2 * L; j++) imma(d[j], a, b[j], cb);
+            // thread (g, t): samples 2t, 2t+1 of row g (d[.][0], d[.][1]) and of row g+8 (d[.][2], d[.][3])
+            float2 z[4];
+#pragma unroll
+            for (int e = 0; e < 4; e++) {
+                z[e].x = combine<L>(__int_as_float(d[0][e]), __int_as_float(d[2][e]), __int_as_float(d[2 * L - 2][e]));
+                z[e].y = combine<L>(__int_as_float(d[1][e]), __int_as_float(d[3][e]), __int_as_float(d[2 * L - 1][e]));
+            }
+            if (DUMP) {
+                const int n = SPAN * warp + 128 * k + 8 * g + 2 * t;
+                z_out[n] = z[0]; z_out[n + 1] = z[1]; z_out[n + 64] = z[2]; z_out[n + 65] = z[3];
+            }
+            // partner of the odd sample: the next lane's even sample (next row for t = 3); lane 31's
+            // lower row continues in lane 0's upper row, lane 31's upper row in the next tile
+            float2 nlo, nhi;
+            nlo.x = __shfl_sync(0xFFFFFFFFu, z[0].x, (lane + 1) & 31); nlo.y = __shfl_sync(0xFFFFFFFFu, z[0].y, (lane + 1) & 31);
+            nhi.x = __shfl_sync(0xFFFFFFFFu, z[2].x, (lane + 1) & 31); nhi.y = __shfl_sync(0xFFFFFFFFu, z[2].y, (lane + 1) & 31);
+            // decisions of this tile's rows 0..7 and of the PREVIOUS tile's rows 8..15 complete here
+            const float2 part_lo = lane == 31 ? nhi : nlo;
+            const float e0 = fmaf(-z[0].y, z[1].y, -z[0].x * z[1].x);
+            const float e1 = fmaf(-z[1].y, part_lo.y, -z[1].x * part_lo.x);
+            const float e2 = fmaf(-z[2].y, z[3].y, -z[2].x * z[3].x);
+            // upper rows: lane 31's partner is the next tile's z[0] of lane 0 -- computed one tile late
+            const float e3 = fmaf(-z[3].y, nhi.y, -z[3].x * nhi.x);          // wrong for lane 31, fixed below
+            const uint32_t E_lo = __ballot_sync(0xFFFFFFFFu, e0 < 0.f), O_lo = __ballot_sync(0xFFFFFFFFu, e1 < 0.f);
+            const uint32_t E_hi = __ballot_sync(0xFFFFFFFFu, e2 < 0.f);
+            uint32_t O_hi = __ballot_sync(0xFFFFFFFFu, e3 < 0.f);
+            // previous tile's last decision: (carry_z, this tile's z[0] of lane 0)
+            const float zx0 = __shfl_sync(0xFFFFFFFFu, z[0].x, 0), zy0 = __shfl_sync(0xFFFFFFFFu, z[0].y, 0);
+            const uint32_t fix = fmaf(-carry_z.y, zy0, -carry_z.x * zx0) < 0.f ? 0x80000000u : 0u;
+            carry_z.x = __shfl_sync(0xFFFFFFFFu, z[3].x, 31); carry_z.y = __shfl_sync(0xFFFFFFFFu, z[3].y, 31);
+            if (lane == 0) {
+                if (k > 0) ballots[warp][k - 1][3] = (ballots[warp][k - 1][3] & 0x7FFFFFFFu) | fix;
+                ballots[warp][k][0] = E_lo; ballots[warp][k][1] = O_lo; ballots[warp][k][2] = E_hi; ballots[warp][k][3] = O_hi;
+                if (k == 0) zx[warp] = z[0];
+            }
+        }
+        __syncwarp();
+        // words i and i + 32 of the span: 28 decisions each; decision d = 128 k + 8 r + s sits in ballot
+        // (r < 8 ? 0 : 2) + (s & 1) of tile k at bit 4 (r & 7) + (s >> 1)
+#pragma unroll
+        for (int wi = 0; wi < 2; wi++) {
+            const int w = lane + 32 * wi;
+            uint32_t word = 0;
+            // 28 consecutive decisions = 14 even + 14 odd ones: bits [h0, h0 + 14) of the even and odd half-streams
+            const int h0 = 14 * w;                                            // index into the 896-bit half-streams
+            const uint32_t *bl = &ballots[warp][0][0];
+            // half-stream bit i of parity q: tile i / 64, ballot (i % 64 < 32 ? 0 : 2) + q, bit i % 32
+            uint32_t ev, od;
+            {
+                const int i0 = h0 >> 5, sh = h0 & 31;
+                const uint32_t e_a = bl[(i0 >> 1) * 4 + (i0 & 1) * 2], e_b = bl[((i0 + 1) >> 1) * 4 + ((i0 + 1) & 1) * 2];
+                const uint32_t o_a = bl[(i0 >> 1) * 4 + (i0 & 1) * 2 + 1], o_b = bl[((i0 + 1) >> 1) * 4 + ((i0 + 1) & 1) * 2 + 1];
+                ev = __funnelshift_r(e_a, e_b, sh) & 0x3FFFu;
+                od = __funnelshift_r(o_a, o_b, sh) & 0x3FFFu;
+            }
+            // interleave 14 + 14 bits
+            uint32_t x = ev, y = od;
+            x = (x | (x << 8)) & 0x00FF00FFu; x = (x | (x << 4)) & 0x0F0F0F0Fu; x = (x | (x << 2)) & 0x33333333u; x = (x | (x << 1)) & 0x55555555u;
+            y = (y | (y << 8)) & 0x00FF00FFu; y = (y | (y << 4)) & 0x0F0F0F0Fu; y = (y | (y << 2)) & 0x33333333u; y = (y | (y << 1)) & 0x55555555u;
+            word = x | (y << 1);
+            if (words_out) words_out[(size_t)blockIdx.x * WARPS * 64 + warp * 64 + w] = word;
+            sink ^= word;
+        }
+        __syncwarp();
+    }
+    const unsigned long long t1 = clock64();
+    if (threadIdx.x == 0) cycles[blockIdx.x] = t1 - t0;
+    if (sink == 0x12345u && words_out) words_out[0] = sink;
+}
+
+template <int L>
+static void run(int reps) {
+    uint8_t *src; uint32_t *words; float2 *z; unsigned long long *cyc;
+    std::vector<uint8_t> h(BUF);
+    uint32_t x = 12345;
+    for (auto &v : h) { x = x * 1664525u + 1013904223u; v = 127 + (int)((x >> 24) & 0x3F) - 32 + (int)(50.0 * sin(0.02 * (&v - h.data()))); }
+    CK(cudaMalloc(&src, BUF)); CK(cudaMemcpy(src, h.data(), BUF, cudaMemcpyHostToDevice));
+    CK(cudaMalloc(&words, 148 * WARPS * 64 * 4)); CK(cudaMalloc(&z, sizeof(float2) * (WARPS * SPAN + 128))); CK(cudaMalloc(&cyc, 148 * 8));
+    // correctness: one CTA, z and words against the host
+    CK(cudaFuncSetAttribute(k_lab<L, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, BUF));
+    CK(cudaFuncSetAttribute(k_lab<L, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, BUF));
+    k_lab<L, true><<<1, WARPS * 32, BUF>>>(src, words, z, 1, cyc);
+    CK(cudaDeviceSynchronize());
+    std::vector<float2> hz(WARPS * SPAN); std::vector<uint32_t> hw(WARPS * 64);
+    CK(cudaMemcpy(hz.data(), z, sizeof(float2) * hz.size(), cudaMemcpyDeviceToHost));
+    CK(cudaMemcpy(hw.data(), words, 4 * hw.size(), cudaMemcpyDeviceToHost));
+    const int T[5] = {tap5<L>(0), tap5<L>(1), tap5<L>(2), tap5<L>(3), tap5<L>(4)};
+    std::vector<double> zr(WARPS * SPAN + 1), zi(WARPS * SPAN + 1);
+    double worst = 0;
+    for (int n = 0; n <= WARPS * SPAN; n++) {
+        double a = 0, bq = 0;
+        for (int m = 0; m < 9; m++) {
+            const double tt = T[m < 5 ? m : 8 - m], xr = h[2 * (n + m + OFF)] - 127.4, xi = h[2 * (n + m + OFF) + 1] - 127.4;
+            switch (m & 3) { case 0: a += tt * xr; bq += tt * xi; break; case 1: a -= tt * xi; bq += tt * xr; break;
+                             case 2: a -= tt * xr; bq -= tt * xi; break; default: a += tt * xi; bq -= tt * xr; }
+        }
+        zr[n] = a; zi[n] = bq;
+        if (n < WARPS * SPAN) worst = fmax(worst, fmax(fabs(hz[n].x - a), fabs(hz[n].y - bq)) / (T[4] * 128.0));
+    }
+    size_t bad_bits = 0, checked = 0;
+    for (int w = 0; w < WARPS * 64; w++)
+        for (int i = 0; i < 28; i++) {
+            const int n = 28 * w + i;
+            if ((n % SPAN) == SPAN - 1) continue;                 // the span's last decision needs the neighbour warp
+            const int want = (zr[n] * zr[n + 1] + zi[n] * zi[n + 1]) > 0.0;
+            bad_bits += ((hw[w] >> i) & 1u) != (uint32_t)want; checked++;
+        }
+    // timing: all SMs
+    k_lab<L, false><<<148, WARPS * 32, BUF>>>(src, words, z, reps, cyc);
+    CK(cudaDeviceSynchronize());
+    unsigned long long hc[148]; CK(cudaMemcpy(hc, cyc, sizeof(hc), cudaMemcpyDeviceToHost));
+    double s = 0; for (int i = 0; i < 148; i++) s += (double)hc[i];
+    s /= 148;
+    const double samples_per_lane = (double)reps * SPAN / 32.0;   // each warp: SPAN samples per repetition
+    printf("L=%d: z worst error %.3g of full scale, %zu of %zu decision bits differ from float64; "
+           "%.2f cycles per sample and lane (%d warps per SM, compute only)\n",
+           L, worst, bad_bits, checked, s / samples_per_lane / (WARPS / 4), WARPS);
+    cudaFree(src); cudaFree(words); cudaFree(z); cudaFree(cyc);
+}
+
+int main() {
+    run<3>(300);
+    run<2>(300);
+    return 0;
+}
