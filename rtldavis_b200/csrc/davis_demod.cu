@@ -123,7 +123,7 @@ __device__ __forceinline__ float2 fir9_pair(const float2 (&r)[39], int q, float 
 
 constexpr int DEMOD_THREADS = DEMOD_WARPS * 32;
 static_assert(2 * DEMOD_THREADS == TILE_WORDS, "two words per thread");
-constexpr int TILE_BYTES = 2 * TILE_SAMPLES;                 // 28672
+constexpr int TILE_BYTES = 2 * TILE_SAMPLES;                 // 57344
 constexpr int HALF_BYTES = TILE_BYTES / 2;                   // run B starts here
 constexpr int LEAD_BYTES = 32;                               // history in front of a tile
 constexpr int BUF_BYTES = TILE_BYTES + LEAD_BYTES + 96;      // padded to a multiple of 128

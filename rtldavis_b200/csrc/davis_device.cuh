@@ -22,7 +22,7 @@ constexpr int HALO = 16;         // extra history samples kept in front of the c
 // decision bitmap: word w of a stream holds samples [28w, 28w+28), bit i = sample 28w+i
 constexpr int LANE_SAMPLES = 2 * SPS;                    // 28 decisions per 32-bit word
 constexpr int TILE_WORDS = 1024;                         // words per demod tile (two per thread)
-constexpr int TILE_SAMPLES = TILE_WORDS * LANE_SAMPLES;  // 14336
+constexpr int TILE_SAMPLES = TILE_WORDS * LANE_SAMPLES;  // 28672
 constexpr int SEARCH_AHEAD = 12;                         // words the search may read past the last tile (keeps rows 16-byte aligned)
 
 // fir9 taps, src/rtldavis/dsp.py:56-69

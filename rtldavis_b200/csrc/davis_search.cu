@@ -7,6 +7,7 @@
 // (dsp.py:190-246; Go dsp/dsp.go:138-169) and the CRC gate of Parser.parse
 // (src/rtldavis/protocol.py:290-300 with crc.py:19-42 and protocol.py:79-83).
 #include <algorithm>
+#include <cstdlib>
 
 #include "davis_kernels.cuh"
 
@@ -26,6 +27,12 @@ namespace davis {
 // The one-symbol slack exists because the bitmap comes from fp32 arithmetic: a
 // true match (in the reference's float64) with one marginal fp32 sign must not
 // be lost.  k_precheck settles such positions in fp64.
+// What the slack does NOT cover: a true match TWO of whose sixteen sync symbols have an
+// fp32 sign different from the float64 one is dropped here, before any exact check.  The
+// fp32 sign differs from the reference's in 2.9e-8 of the samples (5 of 172 M, always where
+// the discriminator is within 1e-5 of zero: profiles/r01_decision_bits_172M_samples_v12.txt),
+// so the probability per packet is ~C(16,2) x (2.9e-8)^2 = 1e-13: no test has met one, and
+// "equal to the reference" holds for every position that reaches k_precheck.
 // ---------------------------------------------------------------------------
 // Grid of a persistent (grid-stride) kernel: as many CTAs as are resident at once.  A CTA
 // that has to wait for a slot starts when the others are done and leaves the GPU mostly
@@ -43,7 +50,9 @@ unsigned int resident_grid(K kernel, int threads, size_t smem = 0) {
     int per_sm = 0;
     if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, threads, smem) != cudaSuccess || per_sm < 1)
         per_sm = 1;
-    return (unsigned int)(sms * per_sm);
+    static int div = 0;                  // lab hook: DAVIS_CHAIN_GRID_DIV=2 halves the chains' grids
+    if (!div) { const char *e = getenv("DAVIS_CHAIN_GRID_DIV"); div = e ? std::max(1, atoi(e)) : 1; }
+    return (unsigned int)(sms * std::max(1, per_sm / div));
 }
 
 constexpr int SEARCH_THREADS = 256;

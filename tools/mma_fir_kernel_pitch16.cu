@@ -1,3 +1,6 @@
+// tools/mma_fir_kernel_pitch16.cu -- LAB RECORD, not product code: variant B1 of profiles/r02_mma_fir_lab.txt
+// (the raw byte stream as the tcgen05 A operand through an overlapping descriptor), as measured in commit
+// 199c4da with that commit's tools/mma_fir_lab.cu.  The current lab drives tools/mma_fir_kernel_pitch64.cu.
 // davis_demod_mma.cu -- the streaming demodulation kernel on the 5th-generation tensor
 // cores (uint8 IQ -> decision bitmap), SURVEY section 7 "hard part 1" contingency.
 //

@@ -1,3 +1,5 @@
+// tools/mma_fir_kernel_pitch64.cu -- LAB RECORD, not product code: variant B2 of profiles/r02_mma_fir_lab.txt.
+// Correct (z and bitmap checked by tools/mma_fir_lab.cu) and slower than the SIMT kernel; not built into the library.
 // davis_demod_mma.cu -- the streaming demodulation kernel on the 5th-generation tensor
 // cores (uint8 IQ -> decision bitmap), SURVEY section 7 "hard part 1" contingency.
 //
