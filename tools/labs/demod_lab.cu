@@ -2,13 +2,13 @@
 // Links the product kernel (davis_demod.cu) as the baseline and times experimental
 // variants against it on the same random input, comparing the decision bitmaps.
 // Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -lineinfo \
-//        -o tools/demod_lab tools/demod_lab.cu rtldavis_b200/csrc/davis_demod.cu
+//        -o tools/labs/demod_lab tools/labs/demod_lab.cu rtldavis_b200/csrc/davis_demod.cu
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <vector>
 
-#include "../rtldavis_b200/csrc/davis_kernels.cuh"
+#include "../../rtldavis_b200/csrc/davis_kernels.cuh"
 #include "demod_lab_variants.cuh"
 
 using namespace davis;

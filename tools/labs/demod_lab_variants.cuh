@@ -3,7 +3,7 @@
 #include <algorithm>
 #include <cstdio>
 
-#include "../rtldavis_b200/csrc/davis_kernels.cuh"
+#include "../../rtldavis_b200/csrc/davis_kernels.cuh"
 
 namespace lab {
 using namespace davis;

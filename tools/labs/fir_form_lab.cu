@@ -6,7 +6,7 @@
 // followed by the cross product (FMUL2 + FFMA2) and two SHF per step.  Same instruction count and
 // the same FMA-pipe cycles; FORM 1 reads fewer registers if the operand-reuse cache serves the
 // shared multiplicand.  Prints cycles per packed step per SMSP (4 warps each).
-// Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -o tools/fir_form_lab tools/fir_form_lab.cu
+// Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -o tools/labs/fir_form_lab tools/labs/fir_form_lab.cu
 #include <cstdint>
 #include <cstdio>
 

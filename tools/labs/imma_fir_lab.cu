@@ -2,7 +2,7 @@
 // legacy warp-level tensor path (mma.sync m16n8k32 u8 x s8 -> s32, SASS IMMA.16832.U8.S8): what does
 // a sample cost in issue cycles when the bytes come from shared memory (no global traffic)?
 // (development tool; the arithmetic is checked against the float64 evaluation on the host)
-// Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -o tools/imma_fir_lab tools/imma_fir_lab.cu
+// Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -o tools/labs/imma_fir_lab tools/labs/imma_fir_lab.cu
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>

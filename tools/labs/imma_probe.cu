@@ -1,7 +1,7 @@
 // imma_probe.cu -- throughput of the legacy warp-level mma.sync (m16n8k32, u8 x s8 -> s32) on sm_100a:
 // cycles per instruction and SM sub-partition with 1..8 warps per sub-partition, alone and next to
 // FFMA work.  (development tool)
-// Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -o tools/imma_probe tools/imma_probe.cu
+// Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -o tools/labs/imma_probe tools/labs/imma_probe.cu
 #include <cstdio>
 #include <cstdlib>
 #include <cstdint>

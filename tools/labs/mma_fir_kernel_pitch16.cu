@@ -1,6 +1,6 @@
-// tools/mma_fir_kernel_pitch16.cu -- LAB RECORD, not product code: variant B1 of profiles/r02_mma_fir_lab.txt
+// tools/labs/mma_fir_kernel_pitch16.cu -- LAB RECORD, not product code: variant B1 of profiles/r02_mma_fir_lab.txt
 // (the raw byte stream as the tcgen05 A operand through an overlapping descriptor), as measured in commit
-// 199c4da with that commit's tools/mma_fir_lab.cu.  The current lab drives tools/mma_fir_kernel_pitch64.cu.
+// 199c4da with that commit's tools/labs/mma_fir_lab.cu.  The current lab drives tools/labs/mma_fir_kernel_pitch64.cu.
 // davis_demod_mma.cu -- the streaming demodulation kernel on the 5th-generation tensor
 // cores (uint8 IQ -> decision bitmap), SURVEY section 7 "hard part 1" contingency.
 //
@@ -50,8 +50,8 @@
 // the SIMT kernel; tests/test_guard_band.py holds the numpy model of this arithmetic.
 #include <algorithm>
 
-#include "../rtldavis_b200/csrc/davis_async.cuh"
-#include "../rtldavis_b200/csrc/davis_kernels.cuh"
+#include "../../rtldavis_b200/csrc/davis_async.cuh"
+#include "../../rtldavis_b200/csrc/davis_kernels.cuh"
 
 namespace davis {
 namespace mma {
@@ -229,7 +229,7 @@ __device__ float2 z_from_bytes(const uint8_t *p) {
     return make_float2(combine<L>(f[0][0], f[0][1], f[0][2]), combine<L>(f[1][0], f[1][1], f[1][2]));
 }
 
-// LAB = 0: the product kernel.  LAB = 1 (tools/mma_fir_lab.cu): the operand strides come from
+// LAB = 0: the product kernel.  LAB = 1 (tools/labs/mma_fir_lab.cu): the operand strides come from
 // the launch (to probe the descriptor semantics) and z can be dumped.  LAB = 2: the epilogue
 // only drains the accumulators (what the copy + MMA + tensor-memory path costs alone).
 template <int L, int LAB>

@@ -1,5 +1,5 @@
-// tools/mma_fir_kernel_pitch64.cu -- LAB RECORD, not product code: variant B2 of profiles/r02_mma_fir_lab.txt.
-// Correct (z and bitmap checked by tools/mma_fir_lab.cu) and slower than the SIMT kernel; not built into the library.
+// tools/labs/mma_fir_kernel_pitch64.cu -- LAB RECORD, not product code: variant B2 of profiles/r02_mma_fir_lab.txt.
+// Correct (z and bitmap checked by tools/labs/mma_fir_lab.cu) and slower than the SIMT kernel; not built into the library.
 // davis_demod_mma.cu -- the streaming demodulation kernel on the 5th-generation tensor
 // cores (uint8 IQ -> decision bitmap), SURVEY section 7 "hard part 1" contingency.
 //
@@ -54,8 +54,8 @@
 // the SIMT kernel; tests/test_guard_band.py holds the numpy model of this arithmetic.
 #include <algorithm>
 
-#include "../rtldavis_b200/csrc/davis_async.cuh"
-#include "../rtldavis_b200/csrc/davis_kernels.cuh"
+#include "../../rtldavis_b200/csrc/davis_async.cuh"
+#include "../../rtldavis_b200/csrc/davis_kernels.cuh"
 
 namespace davis {
 namespace mma {
@@ -241,7 +241,7 @@ struct Walk {
     __device__ __forceinline__ int set_in_stream() const { return j * SETS_PER_TILE + i; }
 };
 
-// LAB = 0: the product kernel.  LAB = 1 (tools/mma_fir_lab.cu): z can be dumped.  LAB = 2: the
+// LAB = 0: the product kernel.  LAB = 1 (tools/labs/mma_fir_lab.cu): z can be dumped.  LAB = 2: the
 // epilogue only drains the accumulators (what copy + re-layout + MMA + tensor memory cost alone).
 template <int LAB>
 __global__ void __launch_bounds__(THREADS, 1)

@@ -5,15 +5,15 @@
 //   2. full size (1024 streams x 328 blocks): time and bit difference of the 3-limb and 2-limb
 //      variants and of their drain-only forms against the SIMT kernel.
 // Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -lineinfo -DDAVIS_MMA_LAB \
-//        -DDAVIS_MBAR_WATCHDOG -o tools/mma_fir_lab tools/mma_fir_lab.cu \
-//        rtldavis_b200/csrc/davis_demod.cu tools/mma_fir_kernel_pitch64.cu
+//        -DDAVIS_MBAR_WATCHDOG -o tools/labs/mma_fir_lab tools/labs/mma_fir_lab.cu \
+//        rtldavis_b200/csrc/davis_demod.cu tools/labs/mma_fir_kernel_pitch64.cu
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <vector>
 
-#include "../rtldavis_b200/csrc/davis_kernels.cuh"
+#include "../../rtldavis_b200/csrc/davis_kernels.cuh"
 
 using namespace davis;
 

@@ -1,12 +1,12 @@
 // mma_probe.cu -- how long does one tcgen05.mma kind::i8 (M = 128, K = 32) take as a function
 // of N and of the shared-memory layout of its operands?  (development tool)
 // One thread per SM issues `reps` MMAs back to back, commits and waits.
-// Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -o tools/mma_probe tools/mma_probe.cu
+// Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -o tools/labs/mma_probe tools/labs/mma_probe.cu
 #include <cstdio>
 #include <cstdlib>
 #include <cstdint>
 #include <cuda_runtime.h>
-#include "../rtldavis_b200/csrc/davis_async.cuh"
+#include "../../rtldavis_b200/csrc/davis_async.cuh"
 using namespace davis;
 #define CK(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { printf("%s: %s\n", #x, cudaGetErrorString(e_)); exit(1); } } while (0)
 

@@ -1,6 +1,6 @@
 // pipe_probe3.cu -- do packed-fp32 and fp64 instructions overlap when their operands are
 // distinct registers (as in the demod body), or only in the 2-operand form of microbench2?
-// Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -o tools/pipe_probe3 tools/pipe_probe3.cu
+// Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -o tools/labs/pipe_probe3 tools/labs/pipe_probe3.cu
 #include <cstdint>
 #include <cstdio>
 

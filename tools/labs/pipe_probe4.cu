@@ -2,7 +2,7 @@
 // register multiplier, HADD2, HMUL2, the half2 compare) beside FFMA / FFMA2 / PRMT, alone and
 // interleaved, to see whether an fp16 first pass of the filter could issue two values per cycle.
 // 16 warps per SM (4 per sub-partition), 8 independent chains per lane.
-// Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -o tools/pipe_probe4 tools/pipe_probe4.cu
+// Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -o tools/labs/pipe_probe4 tools/labs/pipe_probe4.cu
 #include <cstdint>
 #include <cstdio>
 #include <cuda_fp16.h>

@@ -3,7 +3,7 @@
 // pair per instruction (direct-form filter) or one pair shared by eight consecutive instructions
 // (transposed-form filter: the operand-reuse cache serves it), alone and with 1 or 2 PRMT / SHF
 // per FFMA2.  16 warps per SM.
-// Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -o tools/pipe_probe5 tools/pipe_probe5.cu
+// Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -o tools/labs/pipe_probe5 tools/labs/pipe_probe5.cu
 #include <cstdint>
 #include <cstdio>
 

@@ -4,7 +4,7 @@
 // one.  What decides it is the issue rate of IDP.4A on a sub-partition and whether it runs on a
 // pipe beside the FMA pipe.  Measured here: IDP.4A alone, FFMA2 alone, and the two interleaved
 // 1:1 and 2:1, 16 warps per SM, independent accumulators (no dependency stalls).
-// Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -o tools/pipe_probe6 tools/pipe_probe6.cu
+// Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -o tools/labs/pipe_probe6 tools/labs/pipe_probe6.cu
 #include <cstdint>
 #include <cstdio>
 

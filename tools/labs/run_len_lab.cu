@@ -1,6 +1,6 @@
 // run_len_lab.cu -- compute-only probe: the demod body with RUN consecutive samples per run
 // (the product uses 28): longer runs re-convert and re-filter less halo (9 samples per run).
-// Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -o tools/run_len_lab tools/run_len_lab.cu
+// Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -o tools/labs/run_len_lab tools/labs/run_len_lab.cu
 #include <cstdint>
 #include <cstdio>
 #include <cstdlib>

@@ -1,6 +1,6 @@
 // tmem_probe.cu -- tensor-memory load/store throughput per SM (development tool).
 // 16 warps (4 per lane quadrant) each issue `reps` tcgen05.ld (or .st) of 32 / 16 / 8 columns.
-// Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -o tools/tmem_probe tools/tmem_probe.cu
+// Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -o tools/labs/tmem_probe tools/labs/tmem_probe.cu
 #include <cstdio>
 #include <cstdlib>
 #include <cstdint>

@@ -2,7 +2,7 @@
 // are held as packed f32x2 pairs (FMA pipe) and ND further runs are computed in fp64 (the
 // FP64 pipe issues beside the FMA pipe on this part: profiles/r01_demod_lab.txt).
 // Windows are read from shared memory filled once; nothing is copied from global memory.
-// Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -o tools/tri_lab tools/tri_lab.cu
+// Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -o tools/labs/tri_lab tools/labs/tri_lab.cu
 #include <cstdint>
 #include <cstdio>
 #include <cstdlib>
