@@ -28,7 +28,10 @@
 //     values, so it compiles to uniform-datapath instructions and only the copy
 //     instructions themselves are predicated;
 //   * lanes read their two 80-byte windows with ten 8-byte shared loads each (lane
-//     stride 56 B = 7 x 8 B, odd, so the loads are bank-conflict free).
+//     stride 56 B = 7 x 8 B, odd, so the 16 lanes of a half-warp phase hit 16 distinct bank
+//     pairs).  ncu still counts 6.4 % of the shared-memory wavefronts as conflicting
+//     (profiles/r02_k_demod_ncu_full.txt: 4.2 M of 65 M) -- loads meeting the copy engine's
+//     writes of the next tiles; LSU is 5.6 % busy, so it costs nothing measurable.
 //
 // Arithmetic (fp32, signs only)
 //   x = (u - 127.4)/127.6 and the division by |F|^2 + eps are positive scalings
