@@ -7,7 +7,6 @@
 // (dsp.py:190-246; Go dsp/dsp.go:138-169) and the CRC gate of Parser.parse
 // (src/rtldavis/protocol.py:290-300 with crc.py:19-42 and protocol.py:79-83).
 #include <algorithm>
-#include <cstdlib>
 
 #include "davis_kernels.cuh"
 
@@ -50,9 +49,7 @@ unsigned int resident_grid(K kernel, int threads, size_t smem = 0) {
     int per_sm = 0;
     if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, threads, smem) != cudaSuccess || per_sm < 1)
         per_sm = 1;
-    static int div = 0;                  // lab hook: DAVIS_CHAIN_GRID_DIV=2 halves the chains' grids
-    if (!div) { const char *e = getenv("DAVIS_CHAIN_GRID_DIV"); div = e ? std::max(1, atoi(e)) : 1; }
-    return (unsigned int)(sms * std::max(1, per_sm / div));
+    return (unsigned int)(sms * per_sm);
 }
 
 constexpr int SEARCH_THREADS = 256;

@@ -135,6 +135,22 @@ def make_capture(seed: int, n_samples: int, n_packets: int, snr_db: float = 30.0
     return Capture(to_u8(x), packets)
 
 
+def make_sync_flood(n_samples: int, seed: int, snr_db: float = 25.0, df_hz: float = 800.0) -> np.ndarray:
+    """A transmitter that sends the sync word ``CB 89 CB 89 ...`` for the whole capture: every 16th
+    symbol starts a preamble match, at several sample phases.  The reference answers such input
+    (src/rtldavis/dsp.py:171-205); lists sized for the matches of noise overflow on it."""
+    rng = np.random.default_rng(seed)
+    n_bits = n_samples // SPS + 2
+    bits = np.resize(np.unpackbits(np.array([0xCB, 0x89], dtype=np.uint8)), n_bits)
+    nrz = np.repeat(2.0 * bits - 1.0, SPS)[:n_samples]
+    pad = len(_GAUSS) // 2
+    shaped = np.convolve(np.pad(nrz, pad, mode="edge"), _GAUSS, mode="valid")
+    phase = 2 * np.pi * np.cumsum(DEVIATION_HZ * shaped + df_hz - FS / 4.0) / FS
+    sigma = AMPLITUDE / np.sqrt(2.0) * 10 ** (-snr_db / 20.0)
+    x = AMPLITUDE * np.exp(1j * phase) + sigma * (rng.standard_normal(n_samples) + 1j * rng.standard_normal(n_samples))
+    return to_u8(x)
+
+
 def make_batch(n_streams: int, n_samples: int, n_packets: int, snr_db: float = 30.0,
                seed0: int = 0, df_range_hz: float = 0.0, ppm_range: float = 0.0
                ) -> Tuple[np.ndarray, List[List[Embedded]]]:

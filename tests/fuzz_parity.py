@@ -22,8 +22,12 @@ def main():
         snr = float(rng.uniform(2.0, 30.0))
         iq, _ = synth.make_batch(ns, nb * 8192, int(rng.integers(1, 5)), snr, seed0=int(rng.integers(0, 10**6)),
                                  df_range_hz=float(rng.uniform(0, 3000)), ppm_range=float(rng.uniform(0, 50)))
+        flood = nb >= 8 and rng.random() < 0.2       # one stream of nothing but sync words: list re-runs
+        if flood:
+            iq[int(rng.integers(0, ns))] = synth.make_sync_flood(nb * 8192, int(rng.integers(0, 10**6)),
+                                                                 df_hz=float(rng.uniform(-2000, 2000)))
         want = [(int(r["stream"]), int(r["call"]), int(r["index"]), r["data"].tobytes(), bool(r["crc_ok"]))
-                for r in CO.batch_records(iq)]
+                for r in CO.batch_records(iq, per_stream_cap=1 << 16)]
         # random chunking
         cuts, k = [], 0
         while k < nb:
@@ -36,18 +40,20 @@ def main():
             cfg = dsp.PacketConfig(19200, 14, 16, 80, "1100101110001001", block_size=8192, flavor="go")
         else:
             cfg = protocol.new_packet_config(14)
-        bd = dsp.BatchDemodulator(cfg, ns, max_blocks=max(cuts))
-        got, k = [], 0
+        kw = {} if on_dev or rng.random() < 0.5 else {"host_slots": int(rng.integers(1, 4)), "host_group": int(rng.integers(1, ns + 1))}
+        bd = dsp.BatchDemodulator(cfg, ns, max_blocks=max(cuts), **kw)
+        got, k, reruns = [], 0, 0
         for step in cuts:
             part = np.ascontiguousarray(iq[:, k * 16384:(k + step) * 16384])
             bd.submit(torch.from_numpy(part).cuda() if on_dev else part)
             got += rows(bd.fetch())
+            reruns += int(bd.stats().reruns)
             k += step
         bd.close()
         ok = sorted(got) == sorted(want)
         total += len(want)
         print(f"case {c:3d}: streams {ns:4d} blocks {nb:2d} snr {snr:5.1f} cuts {cuts} {'dev' if on_dev else 'host'} {'go' if go else 'py'} "
-              f"records {len(want):5d} {'ok' if ok else 'MISMATCH'}", flush=True)
+              f"records {len(want):5d}{' flood' if flood else ''}{f' reruns {reruns}' if reruns else ''} {'ok' if ok else 'MISMATCH'}", flush=True)
         if not ok:
             sw, sg = set(want), set(got)
             print("  missing", sorted(sw - sg)[:5]); print("  extra", sorted(sg - sw)[:5])

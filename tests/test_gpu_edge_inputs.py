@@ -34,18 +34,8 @@ def _oracle(iq):
 
 
 def sync_word_forever(n_samples, seed, snr_db=25.0, df_hz=800.0):
-    """A transmitter that sends CB 89 CB 89 ... for the whole capture."""
     from rtldavis_b200 import synth
-    rng = np.random.default_rng(seed)
-    n_bits = n_samples // synth.SPS + 2
-    bits = np.resize(np.unpackbits(np.array([0xCB, 0x89], dtype=np.uint8)), n_bits)
-    nrz = np.repeat(2.0 * bits - 1.0, synth.SPS)[:n_samples]
-    pad = len(synth._GAUSS) // 2
-    shaped = np.convolve(np.pad(nrz, pad, mode="edge"), synth._GAUSS, mode="valid")
-    phase = 2 * np.pi * np.cumsum(synth.DEVIATION_HZ * shaped + df_hz - synth.FS / 4.0) / synth.FS
-    sigma = synth.AMPLITUDE / np.sqrt(2.0) * 10 ** (-snr_db / 20.0)
-    x = synth.AMPLITUDE * np.exp(1j * phase) + sigma * (rng.standard_normal(n_samples) + 1j * rng.standard_normal(n_samples))
-    return synth.to_u8(x)
+    return synth.make_sync_flood(n_samples, seed, snr_db, df_hz)
 
 
 def test_a_stream_that_repeats_the_sync_word_is_answered_not_refused(dsp, cfg):
