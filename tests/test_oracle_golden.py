@@ -157,6 +157,28 @@ def test_oracles_match_reference_on_10s_captures(name):
     assert [(p.call, p.index, p.data, p.crc_ok) for p in got_c] == want_rows
 
 
+@pytest.mark.parametrize("name", ["config1_10s", "noise_10s"])
+def test_fixtures_reproduce_from_the_unmodified_reference(name):
+    """The fixtures are what the reference returns: run it again (oracle/_ref or /root/reference)
+    on the regenerated bytes and compare every row and every quantized bit with the stored ones."""
+    from oracle import ref_loader
+    if not ref_loader.available():
+        pytest.skip("the reference is neither staged in oracle/_ref nor at /root/reference")
+    ref_dsp, ref_crc, ref_protocol = ref_loader.load()
+    g, iq = load_seeded(name)
+    B = int(g["block"])
+    dem = ref_dsp.Demodulator(ref_protocol.new_packet_config(14))
+    gate = ref_crc.CRC("CCITT-16", 0, 0x1021, 0)
+    rows, bits = [], []
+    for k in range(int(g["n_blocks"])):
+        for p in dem.demodulate(iq[2 * B * k:2 * B * (k + 1)]):
+            host = bytes(ref_protocol.swap_bit_order(int(b)) for b in p.data)
+            rows.append((k, int(p.index), bytes(p.data), int(gate.checksum(host[2:])) == 0))
+        bits.append(dem.quantized[dem.cfg.buffer_length - B:].copy())
+    assert rows == golden_rows(g)
+    assert (np.concatenate(bits) == np.unpackbits(g["bits"])[: int(g["n_bits"])]).all()
+
+
 def test_config1_fixture_is_what_baseline_states():
     """BASELINE configs[0]: 10 s, station 0, 40 embedded packets, all recovered."""
     g = load_golden("config1_10s")
