@@ -116,6 +116,7 @@ typedef struct davis_stats {
     float host_copy_ms;       /* host time copying packet records back               */
     float host_sort_ms;       /* always 0: ordering (dsp.py:175-186) is done on the device */
     uint64_t reruns;          /* chains run again with larger lists (sync-word-dense input) */
+    uint64_t graph_replays;   /* small calls whose chain went out as one cached CUDA graph   */
 } davis_stats;
 
 DAVIS_API int davis_abi_version(void);

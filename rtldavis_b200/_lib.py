@@ -30,7 +30,8 @@ class DavisStats(C.Structure):
                 ("search_ms", C.c_float), ("finish_ms", C.c_float), ("total_ms", C.c_float),
                 ("h2d_bytes", C.c_uint64), ("d2h_bytes", C.c_uint64),
                 ("host_submit_ms", C.c_float), ("host_wait_ms", C.c_float),
-                ("host_copy_ms", C.c_float), ("host_sort_ms", C.c_float), ("reruns", C.c_uint64)]
+                ("host_copy_ms", C.c_float), ("host_sort_ms", C.c_float), ("reruns", C.c_uint64),
+                ("graph_replays", C.c_uint64)]
 
 
 HIT_DTYPE = np.dtype([("position", "<i8"), ("stream", "<u4"), ("call", "<u4"), ("index", "<i4"),

@@ -48,6 +48,7 @@ struct Group {
     const uint8_t *dev_input = nullptr;  // first stream of the group on the device
     size_t dev_stride = 0;
     bool shared_demod = false;           // the bitmap came from a launch that covers several groups
+    bool graph_events = false;           // ev[] belong to a cached CUDA graph, not to the event pool
     cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
 };
 
@@ -78,6 +79,18 @@ struct davis_handle {
     // the queued call, kept for a second run of a group's chain (list overflow)
     const uint8_t *q_iq = nullptr;  size_t q_bytes = 0, q_stride = 0;  bool q_on_device = false;
     std::vector<davis_hit *> retry_hits;                    // larger packet buffers of re-run groups
+    // Small calls (the single-stream, one-block drop-in above all) are launch-bound: five
+    // memsets + nine kernels + the counter copy.  Their chain is captured once per
+    // (blocks, carry buffer, input pointer) into a CUDA graph and replayed.
+    struct ChainGraph {
+        int n_blocks = 0, cur = 0;
+        const uint8_t *dev_input = nullptr;  size_t dev_stride = 0;
+        uint64_t epoch = 0, launches = 0;
+        cudaGraphExec_t exec = nullptr;
+        cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+    };
+    std::vector<ChainGraph> graphs;
+    uint64_t alloc_epoch = 0;                               // bumped whenever a device buffer moves
     bool have_results = false;
     size_t n_results = 0;
     davis_hit *h_hits = nullptr;  size_t h_hits_cap = 0;       // pinned; the fetched packets
@@ -115,6 +128,7 @@ int fail(davis_handle *h, int code, const std::string &msg) {
 template <typename T>
 int grow(davis_handle *h, T **p, size_t *have, size_t want) {
     if (*have >= want) return DAVIS_OK;
+    h->alloc_epoch++;
     if (*p) CU(cudaFree(*p));
     *p = nullptr; *have = 0;
     CU(cudaMalloc((void **)p, want * sizeof(T)));
@@ -180,8 +194,10 @@ void release_groups(davis_handle *h) {
     for (auto &e : h->demod_ev)
         if (e) { h->event_pool.push_back(e); e = nullptr; }
     for (auto &g : h->groups)
-        for (auto &e : g.ev)
-            if (e) { h->event_pool.push_back(e); e = nullptr; }
+        for (auto &e : g.ev) {
+            if (e && !g.graph_events) h->event_pool.push_back(e);
+            e = nullptr;
+        }
     h->groups.clear();
     for (auto p : h->retry_hits) cudaFree(p);
     h->retry_hits.clear();
@@ -193,7 +209,10 @@ void release_groups(davis_handle *h) {
 // chain then starts at the search and waits for that event first (its memsets do not).
 int run_group(davis_handle *h, Stage &stage, Group &g, int gi, const uint8_t *dev_input,
               size_t input_stride, int n_blocks, cudaStream_t st, cudaEvent_t demod_done = nullptr,
-              int cur = -1) {
+              int cur = -1, bool timed = true) {
+    // timed = false while the chain is being captured into a graph: an event whose last record was
+    // captured cannot be waited on or read; run_group_cached records around the graph launch
+    auto mark = [&](int i) -> cudaError_t { return timed ? cudaEventRecord(g.ev[i], st) : cudaSuccess; };
     if (cur < 0) cur = h->cur;           // which carry buffer holds the state BEFORE this call
     g.dev_input = dev_input;
     g.dev_stride = input_stride;
@@ -236,15 +255,15 @@ int run_group(davis_handle *h, Stage &stage, Group &g, int gi, const uint8_t *de
     if (!g.planes) g.planes = stage.planes;
     if (demod_done) {
         CU(cudaStreamWaitEvent(st, demod_done, 0));
-        CU(cudaEventRecord(g.ev[0], st));
+        CU(mark(0));
     } else {
-        CU(cudaEventRecord(g.ev[0], st));
+        CU(mark(0));
         if (bytes_in) launch_demod(vw, g.planes, g.ns, stage.tiles, stage.words_alloc, nullptr, 0, st);
         else launch_exact_all(vw, sp, g.planes, st);               // complex input: fp64 decisions throughout
     }
-    CU(cudaEventRecord(g.ev[1], st));
+    CU(mark(1));
     launch_search(g.planes, sp, stage.cand, stage.ctr, st);
-    CU(cudaEventRecord(g.ev[2], st));
+    CU(mark(2));
     launch_precheck(vw, sp, stage.cand, stage.conf, stage.marks, stage.glist, stage.ctr, !bytes_in, st);
     if (bytes_in) launch_exact(vw, sp, g.planes, stage.glist, stage.fixes, stage.ctr, st);
     launch_slice(vw, sp, g.planes, stage.conf, stage.fixes, stage.recs, stage.tbl, stage.lost,
@@ -257,12 +276,74 @@ int run_group(davis_handle *h, Stage &stage, Group &g, int gi, const uint8_t *de
                  h->carry[cur ^ 1] + (size_t)g.s0 * h->carry_stride, h->carry_stride, h->n_keep,
                  dev_input, input_stride, n_blocks * h->B, g.ns, h->d_blocks_done + g.s0, n_blocks,
                  h->elem, st);
-    CU(cudaEventRecord(g.ev[3], st));
+    CU(mark(3));
     CU(cudaMemcpyAsync(&h->h_ctr[gi], stage.ctr, sizeof(Counters), cudaMemcpyDeviceToHost, st));
-    CU(cudaEventRecord(g.ev[4], st));
+    CU(mark(4));
     CU(cudaGetLastError());
     stage.last_group = gi;
     h->stats.launches += (demod_done ? 8 : 9) + (uint64_t)((g.ns + 65534) / 65535);
+    return DAVIS_OK;
+}
+
+// A small call's chain through a cached CUDA graph: captured from run_group the first time a
+// (blocks, carry buffer, input pointer) combination is seen, replayed afterwards.
+int run_group_cached(davis_handle *h, Stage &stage, Group &g, int gi, const uint8_t *dev_input,
+                     size_t input_stride, int n_blocks, cudaStream_t st) {
+    davis_handle::ChainGraph *cg = nullptr;
+    for (auto &c : h->graphs)
+        if (c.n_blocks == n_blocks && c.cur == h->cur && c.dev_input == dev_input && c.dev_stride == input_stride) {
+            cg = &c;
+            break;
+        }
+    if (!cg) {
+        if (h->graphs.size() >= 16) {                      // callers cycling through many input buffers
+            auto &old = h->graphs.front();
+            if (old.exec) cudaGraphExecDestroy(old.exec);
+            for (auto e : old.ev) if (e) h->event_pool.push_back(e);
+            h->graphs.erase(h->graphs.begin());
+        }
+        h->graphs.emplace_back();
+        cg = &h->graphs.back();
+        cg->n_blocks = n_blocks; cg->cur = h->cur; cg->dev_input = dev_input; cg->dev_stride = input_stride;
+        for (auto &e : cg->ev) { const int rc = get_event(h, &e); if (rc) return rc; }
+    }
+    if (cg->exec && cg->epoch != h->alloc_epoch) {          // a buffer the graph points at has moved
+        cudaGraphExecDestroy(cg->exec);
+        cg->exec = nullptr;
+    }
+    for (auto &e : g.ev) { if (e && !g.graph_events) h->event_pool.push_back(e); e = nullptr; }
+    for (int i = 0; i < 5; i++) g.ev[i] = cg->ev[i];
+    g.graph_events = true;
+    if (!cg->exec) {
+        const uint64_t before = h->stats.launches;
+        CU(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+        const int rc = run_group(h, stage, g, gi, dev_input, input_stride, n_blocks, st, nullptr, -1, false);
+        cudaGraph_t graph = nullptr;
+        const cudaError_t e = cudaStreamEndCapture(st, &graph);
+        if (rc || e != cudaSuccess) {
+            if (graph) cudaGraphDestroy(graph);
+            cudaGetLastError();
+            return rc ? rc : fail(h, DAVIS_E_CUDA, std::string("stream capture: ") + cudaGetErrorString(e));
+        }
+        const cudaError_t ei = cudaGraphInstantiate(&cg->exec, graph, 0);
+        cudaGraphDestroy(graph);
+        if (ei != cudaSuccess) { cg->exec = nullptr; return fail(h, DAVIS_E_CUDA, cudaGetErrorString(ei)); }
+        cg->launches = h->stats.launches - before;
+        cg->epoch = h->alloc_epoch;
+    } else {                                                // what run_group notes on the host
+        g.dev_input = dev_input;
+        g.dev_stride = input_stride;
+        g.shared_demod = false;
+        g.hits = h->d_hits + g.hit_off;
+        g.planes = stage.planes;
+        stage.last_group = gi;
+        h->stats.launches += cg->launches;
+    }
+    // per-kernel times are not taken in this mode: the whole chain counts as "finish"
+    for (int i = 0; i < 3; i++) CU(cudaEventRecord(g.ev[i], st));
+    CU(cudaGraphLaunch(cg->exec, st));
+    for (int i = 3; i < 5; i++) CU(cudaEventRecord(g.ev[i], st));
+    h->stats.graph_replays += 1;
     return DAVIS_OK;
 }
 
@@ -317,7 +398,10 @@ int davis_create(const davis_cfg *cfg, int n_streams, int device, davis_handle *
     for (int i = 0; i < 2; i++) {
         if (cudaMalloc((void **)&h->carry[i], h->carry_stride * n_streams) != cudaSuccess)
             return bail(DAVIS_E_NOMEM);
-        cudaMemset(h->carry[i], 0, h->carry_stride * n_streams);
+        // history of a fresh stream: the reference starts from zero samples (dsp.py:129-134); byte
+        // 127 is the nearest a uint8 sample gets to zero (-0.003).  Only the streaming kernel's
+        // candidate bits of global samples < 10 see it; every exact path substitutes true zeros.
+        cudaMemset(h->carry[i], 127, h->carry_stride * n_streams);
     }
     if (cudaMalloc((void **)&h->d_blocks_done, sizeof(int64_t) * n_streams) != cudaSuccess)
         return bail(DAVIS_E_NOMEM);
@@ -341,6 +425,11 @@ int davis_destroy(davis_handle *h) {
     cudaSetDevice(h->device);
     cudaDeviceSynchronize();
     release_groups(h);
+    for (auto &c : h->graphs) {
+        if (c.exec) cudaGraphExecDestroy(c.exec);
+        for (auto e : c.ev) if (e) cudaEventDestroy(e);
+    }
+    h->graphs.clear();
     for (auto e : h->event_pool) cudaEventDestroy(e);
     for (auto &s : h->stages) {
         if (s.staging) cudaFree(s.staging);
@@ -373,12 +462,19 @@ int davis_reset(davis_handle *h, int stream) {
     if (!h || stream < -1 || stream >= h->n_streams) return fail(h, DAVIS_E_INVAL, "bad stream");
     CU(cudaSetDevice(h->device));
     CU(cudaDeviceSynchronize());
+    // the carried tail goes back to "no history" too (what is left of the previous stream would
+    // only reach the streaming kernel's candidate bits of the first ten samples, but it costs
+    // nothing to keep a reset stream identical to a fresh one)
+    const int fill = h->elem == 2 ? 127 : 0;
     if (stream < 0) {
         std::fill(h->h_blocks_done.begin(), h->h_blocks_done.end(), 0);
         CU(cudaMemset(h->d_blocks_done, 0, sizeof(int64_t) * h->n_streams));
+        for (int i = 0; i < 2; i++) CU(cudaMemset(h->carry[i], fill, h->carry_stride * h->n_streams));
     } else {
         h->h_blocks_done[stream] = 0;
         CU(cudaMemset(h->d_blocks_done + stream, 0, sizeof(int64_t)));
+        for (int i = 0; i < 2; i++)
+            CU(cudaMemset(h->carry[i] + (size_t)stream * h->carry_stride, fill, h->carry_stride));
     }
     h->queued = false;
     h->have_results = false;
@@ -406,9 +502,10 @@ static int set_elem(davis_handle *h, int elem) {
             cudaGetLastError();
             return fail(h, DAVIS_E_NOMEM, "carry buffers for the new input type");
         }
-        cudaMemset(fresh[i], 0, stride * h->n_streams);
+        cudaMemset(fresh[i], elem == 2 ? 127 : 0, stride * h->n_streams);
     }
     for (int i = 0; i < 2; i++) { cudaFree(h->carry[i]); h->carry[i] = fresh[i]; }
+    h->alloc_epoch++;
     h->carry_stride = stride;
     h->elem = elem;
     h->cur = 0;
@@ -490,6 +587,7 @@ static int demod_common(davis_handle *h, const uint8_t *iq, size_t bytes_per_str
     if (h->h_ctr_cap < (size_t)n_groups) {
         if (h->h_ctr) CU(cudaFreeHost(h->h_ctr));
         h->h_ctr = nullptr; h->h_ctr_cap = 0;
+        h->alloc_epoch++;
         CU(cudaHostAlloc((void **)&h->h_ctr, sizeof(Counters) * n_groups, cudaHostAllocDefault));
         h->h_ctr_cap = n_groups;
     }
@@ -560,7 +658,10 @@ static int demod_common(davis_handle *h, const uint8_t *iq, size_t bytes_per_str
             dev_in = stage.staging;
             dev_stride = bytes_per_stream;
         }
-        if ((rc = run_group(h, stage, g, gi, dev_in, dev_stride, n_blocks, st))) return rc;
+        const bool small = n_groups == 1 && (size_t)h->n_streams * (size_t)n_blocks <= 512;
+        if ((rc = small ? run_group_cached(h, stage, g, gi, dev_in, dev_stride, n_blocks, st)
+                        : run_group(h, stage, g, gi, dev_in, dev_stride, n_blocks, st)))
+            return rc;
     }
     }
     h->cur ^= 1;

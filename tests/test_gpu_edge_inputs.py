@@ -165,3 +165,23 @@ def test_going_on_after_a_caller_sized_buffer_overflowed(dsp, cfg):
             assert [(p.index, p.data.tobytes()) for p in out[s][0]] == \
                    [(p.index, p.data) for p in whole[s] if p.call == k]
     bd.close()
+
+
+def test_small_calls_replay_a_cached_graph_and_stay_exact(dsp, cfg):
+    """One block of one stream is launch-bound: its chain is captured into a CUDA graph once per
+    carry buffer and replayed.  Same packets as the oracle, block by block, across a buffer
+    re-allocation (a larger call in between) and a flood that forces a direct re-run."""
+    from rtldavis_b200 import synth
+    iq = synth.make_capture(4100, 40 * B, 10, 20.0, df_hz=1200.0).iq
+    iq[2 * B * 20: 2 * B * 30] = synth.make_sync_flood(10 * B, 7)[: 2 * B * 10]
+    want = _oracle(iq.reshape(1, -1))
+    bd = dsp.BatchDemodulator(cfg, 1, max_blocks=10)
+    got, replays, k = [], 0, 0
+    for take in [1] * 12 + [8] + [1] * 20:                     # 12 + 8 + 20 = 40 blocks
+        bd.submit(iq[2 * B * k: 2 * B * (k + take)].reshape(1, -1))
+        got += _rows(bd.fetch())
+        replays += int(bd.stats().graph_replays)
+        k += take
+    assert k == 40 and got == want
+    assert replays >= 30
+    bd.close()
