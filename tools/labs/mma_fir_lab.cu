@@ -1,9 +1,10 @@
 // mma_fir_lab.cu -- lab for the tensor-core demodulation kernel (development tool).
-//   1. small case: the filter outputs z[n] of davis_demod_mma.cu against a float64 evaluation on
-//      the host (is the overlapping-row operand descriptor accepted? which stride is which?),
-//      and its decision bitmap against the SIMT kernel's (davis_demod.cu);
-//   2. full size (1024 streams x 328 blocks): time and bit difference of the 3-limb and 2-limb
-//      variants and of their drain-only forms against the SIMT kernel.
+//   1. small cases: the filter outputs z[n] of mma_fir_kernel_pitch64.cu against a float64 evaluation
+//      on the host, and its decision bitmap against the SIMT kernel's (davis_demod.cu);
+//   2. full size (1024 streams x 328 blocks): time and bit difference against the SIMT kernel, the
+//      drain-only form, and the cycles every warp role spends per phase.
+//   (Commit 199c4da holds the version of this file that drove mma_fir_kernel_pitch16.cu, with the
+//   2-limb variant and the check of which descriptor stride is which.)
 // Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -lineinfo -DDAVIS_MMA_LAB \
 //        -DDAVIS_MBAR_WATCHDOG -o tools/labs/mma_fir_lab tools/labs/mma_fir_lab.cu \
 //        rtldavis_b200/csrc/davis_demod.cu tools/labs/mma_fir_kernel_pitch64.cu
