@@ -189,6 +189,35 @@ DAVIS_API int davis_debug_bits(davis_handle *h, int stream, uint8_t *out, size_t
 DAVIS_API int davis_debug_disc(davis_handle *h, int stream, double *out, size_t cap);
 DAVIS_API int davis_debug_disc32(davis_handle *h, int stream, float *out, size_t cap);
 
+/* No counterpart in the reference: rtldavis never has to think about device memory.
+ * davis_disc32_static is davis_debug_disc32 for callers that must not allocate on the
+ * GPU -- a receive thread on the dongle's callback deadline (cudaMalloc/cudaFree take a
+ * process-wide lock and can wait for the device to drain), a plug-in in a process whose
+ * device memory belongs to another allocator's pool, a process held to a fixed memory
+ * budget.  It needs no handle and calls neither cudaMalloc nor cudaFree nor anything that
+ * does: its working memory (16 samples of history, the decision bitmap the kernel always
+ * stores, a staging row) is a fixed array of just over 1 MiB inside the library image,
+ * present on every GPU that loads the library until the process exits.
+ *   in   iq_dev    device memory, 16-byte aligned: interleaved I,Q bytes, the FIRST n_samples
+ *                  samples of a stream (zero history in front, like a fresh Demodulator)
+ *   out  out_dev   device memory: n_samples floats, the fp32 streaming kernel's
+ *                  discriminator of those samples (the values davis_debug_disc32 reports)
+ *   n_samples      a multiple of 8, at most DAVIS_STATIC_MAX_SAMPLES (about one second of
+ *                  one channel); more is DAVIS_E_SIZE, nothing is run
+ *   device, cuda_stream   the GPU both buffers live on; the stream the work is put on
+ *                  (NULL = the default stream).  The call returns once the work is
+ *                  enqueued: out_dev is complete when that stream has caught up.
+ *   err, err_cap   optional buffer for the reason of a failure (there is no handle to ask)
+ * The first call on each GPU looks up where the array lives there (cudaGetSymbolAddress);
+ * make that call before any stream capture is begun.  Every call on a GPU uses the same
+ * array and finds the previous call's bytes in it; the entry point rewrites what it relies
+ * on, so calls that follow one another on a stream are independent, but two calls that can
+ * run on the GPU at the same time (different streams, different threads) overwrite each
+ * other's working memory and both results are garbage: serialise them. */
+#define DAVIS_STATIC_MAX_SAMPLES 262144
+DAVIS_API int davis_disc32_static(const uint8_t *iq_dev, size_t n_samples, float *out_dev,
+                        int device, void *cuda_stream, char *err, size_t err_cap);
+
 /* Pinned host memory for pipelined host input (cudaHostAlloc / cudaFreeHost). */
 DAVIS_API int davis_host_alloc(void **p, size_t bytes);
 DAVIS_API int davis_host_free(void *p);

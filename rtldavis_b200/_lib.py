@@ -43,7 +43,7 @@ EXPORTS = ["davis_abi_version", "davis_create", "davis_destroy", "davis_reset", 
            "davis_demod_c64", "davis_demod_c128", "davis_fetch_hits", "davis_fetch_hits_view", "davis_get_stats", "davis_debug_bits",
            "davis_debug_disc", "davis_debug_disc32", "davis_host_alloc", "davis_host_free",
            "davis_crc16_batch", "davis_last_error", "davis_strerror",
-           "davis_synth_fill", "davis_synth_truth"]
+           "davis_synth_fill", "davis_synth_truth", "davis_disc32_static"]
 
 _lib = None
 
@@ -85,6 +85,7 @@ def load() -> C.CDLL:
     L.davis_debug_bits.argtypes = [vp, i32, vp, sz, C.POINTER(C.c_int64), C.POINTER(sz)]
     L.davis_debug_disc.argtypes = [vp, i32, vp, sz]
     L.davis_debug_disc32.argtypes = [vp, i32, vp, sz]
+    L.davis_disc32_static.argtypes = [vp, sz, vp, i32, vp, C.c_char_p, sz]
     L.davis_host_alloc.argtypes = [C.POINTER(vp), sz]
     L.davis_host_free.argtypes = [vp]
     L.davis_crc16_batch.argtypes = [vp, sz, sz, C.c_uint16, C.c_uint16, i32, i32, vp]

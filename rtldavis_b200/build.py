@@ -10,7 +10,8 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB_DIR = os.path.join(HERE, "lib")
 LIB_PATH = os.path.join(LIB_DIR, "libdavis_b200.so")
-SOURCES = ["davis_demod.cu", "davis_search.cu", "davis_capi.cu", "davis_synth.cu"]
+SOURCES = ["davis_demod.cu", "davis_search.cu", "davis_capi.cu", "davis_synth.cu",
+           "davis_static.cu"]
 HEADERS = ["davis_device.cuh", "davis_kernels.cuh", "davis_async.cuh", os.path.join("..", "..", "include", "davis_b200.h")]
 
 NVCC_FLAGS = [
