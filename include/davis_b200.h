@@ -58,7 +58,7 @@ typedef struct davis_cfg {
     uint32_t preamble;         /* sync pattern, first symbol in the MSB: 0xCB89     */
     int32_t block_size;        /* samples per block: 8192 (Python) or 512 (Go)      */
     int32_t max_blocks;        /* largest n_blocks a call will pass (>= 1)          */
-    int32_t max_hits;          /* most packets one call may return (DAVIS_E_OVERFLOW beyond); 0 = no limit */
+    int32_t max_hits;          /* most packets one call may return (first fetch: DAVIS_E_OVERFLOW beyond); 0 = no limit */
     int32_t host_slots;        /* pipeline depth for host-memory input; 0 = auto    */
     int32_t host_group;        /* streams per pipeline stage for host input; 0=auto */
     int32_t flavor;            /* DAVIS_FLAVOR_PYTHON (0) or DAVIS_FLAVOR_GO (1), ABI >= 2 */
@@ -135,8 +135,11 @@ DAVIS_API int davis_reset(davis_handle *h, int stream);
  * stream.  `iq` is interleaved I,Q bytes; stream s starts at iq + s*stream_stride
  * and supplies bytes_per_stream = n_blocks * 2 * block_size bytes (anything else
  * is DAVIS_E_SIZE).  `iq` may be device memory (16-byte aligned, stride a multiple
- * of 16; used in place, must stay valid until the fetch) or host memory (pinned
- * for overlap; staged through the handle's pipeline).  Work is enqueued
+ * of 16; used in place) or host memory (pinned for overlap; staged through the handle's
+ * pipeline).  Either kind must stay valid AND unmodified until the fetch: device input is
+ * read in place by the whole chain, and host input may be copied a second time at the
+ * fetch when a pipeline stage's lists overflowed after a later group of streams had
+ * taken over its staging buffer (davis_stats.reruns).  Work is enqueued
  * asynchronously; `cuda_stream` (a cudaStream_t, may be NULL) is the stream the
  * caller's device input is ordered on. */
 DAVIS_API int davis_demod_u8(davis_handle *h, const uint8_t *iq, size_t bytes_per_stream,
@@ -165,9 +168,10 @@ DAVIS_API int davis_demod_c128(davis_handle *h, const double *iq, size_t samples
  * matches far more often (a transmitter repeating the sync word) makes the library run
  * the affected chain again with larger lists (davis_stats.reruns) -- the reference
  * answers such input (dsp.py:171-205), so does this.  The one remaining overflow error
- * is a packet buffer the caller sized too small with davis_cfg.max_hits > 0: it is
- * reported, never truncated, but the streams have advanced past the call by then
- * (its packets are lost; davis_reset, or go on). */
+ * is a limit the caller set with davis_cfg.max_hits > 0: the fetch that finds more
+ * packets than that returns DAVIS_E_OVERFLOW once, with *n set and nothing copied or
+ * truncated.  The packets are kept (the streams have advanced past the call, so they
+ * could not be produced again): the next fetch hands them out. */
 DAVIS_API int davis_fetch_hits(davis_handle *h, davis_hit *out, size_t cap, size_t *n);
 
 /* Same, without the copy: *out points at the handle's own (pinned) result buffer,

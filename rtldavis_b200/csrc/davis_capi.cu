@@ -90,6 +90,7 @@ struct davis_handle {
         cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
     };
     std::vector<ChainGraph> graphs;
+    int graph_misses = 0;                                   // cache misses in a row with the cache full
     uint64_t alloc_epoch = 0;                               // bumped whenever a device buffer moves
     bool have_results = false;
     size_t n_results = 0;
@@ -295,7 +296,15 @@ int run_group_cached(davis_handle *h, Stage &stage, Group &g, int gi, const uint
             cg = &c;
             break;
         }
+    if (cg) h->graph_misses = 0;
     if (!cg) {
+        // A caller that hands in a fresh device buffer every time (buffers straight from an
+        // allocator) never hits the cache: capture + instantiate + destroy per call costs more
+        // than the chain launched directly.  Once the cache is full and nothing but misses has
+        // been seen for a while, small calls go out as plain launches until a known buffer returns.
+        // (every 64th miss is still captured, so a new working set of buffers finds its way in)
+        if (h->graphs.size() >= 16 && ++h->graph_misses > 16 && h->graph_misses % 64)
+            return run_group(h, stage, g, gi, dev_input, input_stride, n_blocks, st);
         if (h->graphs.size() >= 16) {                      // callers cycling through many input buffers
             auto &old = h->graphs.front();
             if (old.exec) cudaGraphExecDestroy(old.exec);
@@ -316,10 +325,13 @@ int run_group_cached(davis_handle *h, Stage &stage, Group &g, int gi, const uint
     g.graph_events = true;
     if (!cg->exec) {
         const uint64_t before = h->stats.launches;
-        CU(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
-        const int rc = run_group(h, stage, g, gi, dev_input, input_stride, n_blocks, st, nullptr, -1, false);
+        // captured on the stage's own stream, never the caller's (which may itself be in a
+        // capture, or carry work the graph must not swallow); the graph is launched on `st`
+        cudaStream_t cap = stage.st;
+        CU(cudaStreamBeginCapture(cap, cudaStreamCaptureModeThreadLocal));
+        const int rc = run_group(h, stage, g, gi, dev_input, input_stride, n_blocks, cap, nullptr, -1, false);
         cudaGraph_t graph = nullptr;
-        const cudaError_t e = cudaStreamEndCapture(st, &graph);
+        const cudaError_t e = cudaStreamEndCapture(cap, &graph);
         if (rc || e != cudaSuccess) {
             if (graph) cudaGraphDestroy(graph);
             cudaGetLastError();
@@ -726,10 +738,14 @@ static int rerun_group(davis_handle *h, int gi) {
     launch_rewind(h->d_blocks_done + g.s0, g.ns, n_blocks, st);
     const int cur_before = h->cur ^ 1;                      // demod_common flipped it after enqueueing
     if (!h->q_on_device) {
-        // the staging buffer may hold a later group by now: bring this group's input again
-        CU(cudaMemcpy2DAsync(stage.staging, h->q_bytes, h->q_iq + (size_t)g.s0 * h->q_stride, h->q_stride,
-                             h->q_bytes, g.ns, cudaMemcpyHostToDevice, st));
-        h->stats.h2d_bytes += (uint64_t)h->q_bytes * g.ns;
+        // The staging buffer still holds this group's bytes unless a later group of the same
+        // pipeline stage has been copied over them; only then is the caller's host buffer read a
+        // second time (which is why davis_b200.h asks for it to stay untouched until the fetch).
+        if (stage.last_group != gi) {
+            CU(cudaMemcpy2DAsync(stage.staging, h->q_bytes, h->q_iq + (size_t)g.s0 * h->q_stride, h->q_stride,
+                                 h->q_bytes, g.ns, cudaMemcpyHostToDevice, st));
+            h->stats.h2d_bytes += (uint64_t)h->q_bytes * g.ns;
+        }
         g.planes = nullptr;
         return run_group(h, stage, g, gi, stage.staging, h->q_bytes, n_blocks, st, nullptr, cur_before);
     }
@@ -750,13 +766,6 @@ static int complete_call(davis_handle *h) {
             CU(cudaEventSynchronize(g.ev[4]));
             t_wait += now_ms() - t0;
             const Counters c = h->h_ctr[gi];
-            float ms;
-            CU(cudaEventElapsedTime(&ms, g.ev[0], g.ev[1])); demod += ms;
-            CU(cudaEventElapsedTime(&ms, g.ev[1], g.ev[2])); search += ms;
-            CU(cudaEventElapsedTime(&ms, g.ev[2], g.ev[3])); finish += ms;
-            h->stats.candidates += c.n_cand;
-            h->stats.confirmed += c.n_conf;
-            h->stats.records += c.n_rec;
             if (c.overflow) {
                 // An input that matches the sync word far more often than noise does (a
                 // transmitter repeating it, a test pattern) overflows lists sized for noise.  The
@@ -767,20 +776,22 @@ static int complete_call(davis_handle *h) {
                 gi--;                               // look at the same group again
                 continue;
             }
+            // counters and times of the pass that is kept (a pass discarded for an overflow shows
+            // up in davis_stats.reruns only)
+            float ms;
+            CU(cudaEventElapsedTime(&ms, g.ev[0], g.ev[1])); demod += ms;
+            CU(cudaEventElapsedTime(&ms, g.ev[1], g.ev[2])); search += ms;
+            CU(cudaEventElapsedTime(&ms, g.ev[2], g.ev[3])); finish += ms;
+            h->stats.candidates += c.n_cand;
+            h->stats.confirmed += c.n_conf;
+            h->stats.records += c.n_rec;
             g.n_hit = c.n_hit;
             h->n_results += c.n_hit;
             h->stats.d2h_bytes += sizeof(Counters);
         }
-        if (h->cfg.max_hits > 0 && h->n_results > (size_t)h->cfg.max_hits) {
-            // the one overflow that stays an error: a packet buffer the CALLER sized
-            h->queued = false;
-            char msg[200];
-            snprintf(msg, sizeof msg,
-                     "%zu packets exceed max_hits = %d; the streams have advanced past this call: "
-                     "raise max_hits and davis_reset, or go on without its packets",
-                     h->n_results, h->cfg.max_hits);
-            return fail(h, DAVIS_E_OVERFLOW, msg);
-        }
+        // the one overflow that stays an error: a limit the CALLER set.  It is reported by this
+        // fetch, after the packets are safe in the result buffer: the next fetch hands them out.
+        const bool over_max = h->cfg.max_hits > 0 && h->n_results > (size_t)h->cfg.max_hits;
         if (h->demod_ev[0]) {
             float ms;
             CU(cudaEventElapsedTime(&ms, h->demod_ev[0], h->demod_ev[1]));
@@ -825,6 +836,14 @@ static int complete_call(davis_handle *h) {
         h->stats.d2h_bytes += sizeof(davis_hit) * at;
         h->queued = false;
         h->have_results = true;
+        if (over_max) {
+            char msg[200];
+            snprintf(msg, sizeof msg,
+                     "%zu packets exceed max_hits = %d; they are kept: fetch again (with room for "
+                     "them) to take them, or go on without",
+                     h->n_results, h->cfg.max_hits);
+            return fail(h, DAVIS_E_OVERFLOW, msg);
+        }
     } else if (!h->have_results) {
         return fail(h, DAVIS_E_STATE, "nothing queued");
     }
@@ -834,6 +853,7 @@ static int complete_call(davis_handle *h) {
 int davis_fetch_hits(davis_handle *h, davis_hit *out, size_t cap, size_t *n) {
     if (!h || !n) return DAVIS_E_INVAL;
     const int rc = complete_call(h);
+    if (rc == DAVIS_E_OVERFLOW && h->have_results) *n = h->n_results;      // max_hits: see complete_call
     if (rc) return rc;
     *n = h->n_results;
     if (*n > cap) return fail(h, DAVIS_E_OVERFLOW, "caller buffer smaller than the packet count");
@@ -847,6 +867,7 @@ int davis_fetch_hits_view(davis_handle *h, const davis_hit **out, size_t *n) {
     *out = nullptr;
     *n = 0;
     const int rc = complete_call(h);
+    if (rc == DAVIS_E_OVERFLOW && h->have_results) *n = h->n_results;
     if (rc) return rc;
     *out = h->n_results ? h->h_hits : nullptr;
     *n = h->n_results;

@@ -185,3 +185,90 @@ def test_small_calls_replay_a_cached_graph_and_stay_exact(dsp, cfg):
     assert k == 40 and got == want
     assert replays >= 30
     bd.close()
+
+
+def test_host_input_may_be_overwritten_when_its_staging_copy_is_still_there(dsp, cfg):
+    """a re-run after a list overflow used to read the caller's host buffer a second
+    time at the fetch.  It now does so only when a later group has taken the staging buffer; a
+    one-group call re-runs from the library's own copy, so scribbling over the (pageable) input
+    between submit and fetch changes nothing."""
+    n_blocks = 32
+    iq = sync_word_forever(n_blocks * B, 21).reshape(1, -1)
+    want = _oracle(iq)
+    bd = dsp.BatchDemodulator(cfg, 1, max_blocks=n_blocks)
+    mine = iq.copy()
+    bd.submit(mine)
+    mine[:] = 0x55
+    got = _rows(bd.fetch())
+    st = bd.stats()
+    assert st.reruns >= 1 and got == want
+    assert st.h2d_bytes == iq.size                               # the input crossed the link once
+    bd.close()
+
+
+def test_counters_of_a_rerun_call_are_those_of_the_pass_that_was_kept(dsp, cfg):
+    """candidates / confirmed / records were summed over discarded passes too.  The
+    same call repeated on the same handle (lists already grown, fewer re-runs) must count the same."""
+    n_blocks = 48
+    iq = sync_word_forever(n_blocks * B, 22).reshape(1, -1)
+    bd = dsp.BatchDemodulator(cfg, 1, max_blocks=n_blocks)
+    bd.submit(iq)
+    first = _rows(bd.fetch())
+    a = bd.stats()
+    bd.reset()
+    bd.submit(iq)
+    again = _rows(bd.fetch())
+    b = bd.stats()
+    # (the packet buffer is sized per call, so the repeat still re-runs for that one list)
+    assert a.reruns >= 2 and b.reruns < a.reruns and first == again
+    assert (a.candidates, a.confirmed, a.records) == (b.candidates, b.confirmed, b.records)
+    assert a.confirmed >= len(first)
+    bd.close()
+
+
+def test_packets_beyond_max_hits_are_reported_once_and_kept(dsp, cfg):
+    """the fetch that finds more packets than davis_cfg.max_hits still raises, but
+    the packets are no longer thrown away: the next fetch hands out every one of them."""
+    from rtldavis_b200 import _lib, synth
+    iq, _ = synth.make_batch(4, 10 * B, 6, 30.0, seed0=1500)
+    want = _oracle(iq)
+    assert len(want) > 8
+    bd = dsp.BatchDemodulator(cfg, 4, max_blocks=10, max_hits=8)
+    bd.submit(iq)
+    with pytest.raises(_lib.DavisError) as e:
+        bd.fetch()
+    assert e.value.code == _lib.E_OVERFLOW and "kept" in str(e.value)
+    assert _rows(bd.fetch()) == want
+    assert _rows(bd.fetch()) == want
+    bd.close()
+
+
+def test_small_calls_from_ever_new_device_buffers_stop_capturing_graphs(dsp, cfg):
+    """the graph cache is keyed on the input pointer.  A caller whose every block
+    sits in a fresh device buffer never hits it; after the cache has filled and missed 16 times
+    in a row such calls are launched directly (no capture per call), on the caller's stream or
+    the default one, and stay exact.  A buffer the cache knows is replayed again."""
+    import torch
+    from rtldavis_b200 import synth
+    n = 72
+    iq = synth.make_capture(4300, (n + 1) * B, 18, 20.0, df_hz=-900.0).iq
+    want = _oracle(iq.reshape(1, -1))
+    bd = dsp.BatchDemodulator(cfg, 1, max_blocks=1)
+    side = torch.cuda.Stream()
+    bufs, got, replays = [], [], []
+    for k in range(n):
+        with torch.cuda.stream(side if k % 2 else torch.cuda.current_stream()):
+            d = torch.from_numpy(iq[2 * B * k: 2 * B * (k + 1)].copy()).cuda().reshape(1, -1)
+            bufs.append(d)                                        # kept alive: every pointer is new
+            bd.submit(d, cuda_stream=side.cuda_stream if k % 2 else None)
+        got += _rows(bd.fetch())
+        replays.append(int(bd.stats().graph_replays))
+    # block 72 arrives in the buffer of call 30 (same carry parity), which the cache still holds
+    bufs[30].copy_(torch.from_numpy(iq[2 * B * n:].copy()).reshape(1, -1))
+    torch.cuda.synchronize()
+    bd.submit(bufs[30])
+    got += _rows(bd.fetch())
+    replays.append(int(bd.stats().graph_replays))
+    assert got == want
+    assert sum(replays[:32]) >= 30 and sum(replays[40:60]) == 0 and replays[-1] == 1, replays
+    bd.close()
