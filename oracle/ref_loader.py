@@ -9,6 +9,7 @@ from __future__ import annotations
 
 import importlib
 import importlib.machinery
+import importlib.util
 import os
 import sys
 
@@ -24,8 +25,20 @@ def _ref_hook(path):
     return importlib.machinery.FileFinder(path, (importlib.machinery.SourcelessFileLoader, [".rpyc"]))
 
 
+def _staged_ok() -> bool:
+    """oracle/_ref holds byte-code THIS interpreter can run.  Byte-code is tied to the Python
+    minor version that wrote it (the build container's); on a box with another Python the
+    import would die with "bad magic number", so such files count as absent and the callers
+    skip or fall back to the port instead of crashing."""
+    try:
+        with open(os.path.join(_REF_DIR, "rtldavis", "dsp.rpyc"), "rb") as fh:
+            return fh.read(4) == importlib.util.MAGIC_NUMBER
+    except OSError:
+        return False
+
+
 def _root():
-    if os.path.exists(os.path.join(_REF_DIR, "rtldavis", "dsp.rpyc")):
+    if _staged_ok():
         return _REF_DIR
     if os.path.exists(os.path.join(_SRC_DIR, "rtldavis", "dsp.py")):
         return _SRC_DIR

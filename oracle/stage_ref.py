@@ -19,6 +19,7 @@ Run:  python oracle/stage_ref.py   (or ``make -C oracle ref``); a no-op when
 """
 from __future__ import annotations
 
+import importlib.util
 import os
 import py_compile
 import sys
@@ -49,7 +50,8 @@ def stage(verbose: bool = False) -> bool:
             print(dst)
     with open(os.path.join(HERE, "_ref", "PROVENANCE.txt"), "w") as fh:
         fh.write(f"byte-compiled by oracle/stage_ref.py from {REF_SRC} with Python "
-                 f"{sys.version.split()[0]}; unmodified 2bitoperations/rtldavis modules\n")
+                 f"{sys.version.split()[0]} (byte-code magic {importlib.util.MAGIC_NUMBER.hex()}, which "
+                 f"oracle/ref_loader.py checks before importing); unmodified 2bitoperations/rtldavis modules\n")
     return True
 
 

@@ -225,3 +225,22 @@ def test_signed_zero_after_reset():
         assert bits[0] == 0
         assert bits[1] == (1 if (i < 127.4 and q > 127.4) else 0)
         assert (CO.stream_bits(iq)[:16] == bits[:16]).all()
+
+
+def test_staged_reference_of_another_python_counts_as_absent(tmp_path, monkeypatch):
+    """oracle/_ref is byte-code of the build container's Python.  On a box with
+    another minor version the loader must say "not available" (callers then skip or time the
+    port) instead of failing inside the import with "bad magic number"."""
+    import importlib.util
+
+    from oracle import ref_loader
+    fake = tmp_path / "_ref" / "rtldavis"
+    fake.mkdir(parents=True)
+    (fake / "dsp.rpyc").write_bytes(b"\x00\x00\r\n" + b"\x00" * 12)        # not this interpreter's magic
+    monkeypatch.setattr(ref_loader, "_REF_DIR", str(tmp_path / "_ref"))
+    monkeypatch.setattr(ref_loader, "_SRC_DIR", str(tmp_path / "nowhere"))
+    assert not ref_loader.available() and ref_loader.kind() == "port"
+    with pytest.raises(ImportError):
+        ref_loader.load()
+    (fake / "dsp.rpyc").write_bytes(importlib.util.MAGIC_NUMBER + b"\x00" * 12)
+    assert ref_loader.available() and ref_loader.kind() == "ref"
