@@ -84,6 +84,19 @@ def _device_pointer(x):
     return None
 
 
+_UNSUPPORTED = ("unsupported PacketConfig for the B200 demodulator "
+                "(needs symbol_length 14, 16-symbol preamble, 80-symbol packet, "
+                "block_size a multiple of 8 and >= 256)")
+
+
+def _check_supported(cfg: "PacketConfig") -> None:
+    """davis_create's configuration checks (davis_capi.cu), made without touching CUDA."""
+    cfg._to_c(1)                                              # preamble string
+    if (cfg.symbol_length != 14 or cfg.preamble_symbols != 16 or cfg.packet_symbols != 80
+            or cfg.block_size < 256 or cfg.block_size % 8):
+        raise ValueError(_UNSUPPORTED)
+
+
 class BatchDemodulator:
     """``n_streams`` independent reference Demodulators advanced together.
 
@@ -108,9 +121,7 @@ class BatchDemodulator:
         if rc != 0:
             self._h = C.c_void_p()
             if rc == _lib.E_INVAL:
-                raise ValueError("unsupported PacketConfig for the B200 demodulator "
-                                 "(needs symbol_length 14, 16-symbol preamble, 80-symbol packet, "
-                                 "block_size a multiple of 8 and >= 256)")
+                raise ValueError(_UNSUPPORTED)
             check(rc)
         self._keepalive = None
         self._last_blocks = 0
@@ -272,9 +283,26 @@ class Demodulator:
     """dsp.Demodulator, src/rtldavis/dsp.py:127-253: one stream, one block per call."""
 
     def __init__(self, cfg: PacketConfig, device: int = 0) -> None:
+        # Nothing here touches CUDA.  rtldavis builds a Parser (and with it a Demodulator) in the
+        # parent process just to read ``p.cfg`` and the hop tables (runners/rtlsdr.py:30), then
+        # forks the DSP worker (rtlsdr.py:61-65, start method "fork": __main__.py:277), which
+        # builds its own (worker.py:28).  A CUDA context created before the fork would make every
+        # CUDA call in the child fail, so the device handle is created by the first call that
+        # needs it -- in whichever process makes that call.  The library itself is loaded now
+        # (no CPU fallback: a missing libdavis_b200.so fails here, not at the first block), and an
+        # unsupported configuration is refused now as well.
         self.cfg = cfg
-        self._batch = BatchDemodulator(cfg, n_streams=1, device=device, max_blocks=1)
+        self.device = int(device)
+        _lib.load()
+        _check_supported(cfg)
+        self._lazy: Optional[BatchDemodulator] = None
         self._last_hits = np.empty(0, dtype=HIT_DTYPE)
+
+    @property
+    def _batch(self) -> BatchDemodulator:
+        if self._lazy is None:
+            self._lazy = BatchDemodulator(self.cfg, n_streams=1, device=self.device, max_blocks=1)
+        return self._lazy
 
     def demodulate(self, input_data: np.ndarray) -> List[Packet]:
         arr = np.asarray(input_data)
@@ -301,7 +329,10 @@ class Demodulator:
         return self._last_hits
 
     def reset(self) -> None:
-        self._batch.reset(-1)
+        if self._lazy is not None:                           # a stream that never ran has no history
+            self._lazy.reset(-1)
 
     def close(self) -> None:
-        self._batch.close()
+        if self._lazy is not None:
+            self._lazy.close()
+            self._lazy = None

@@ -70,9 +70,14 @@ def _no_gpu():
 @pytest.mark.skipif(not _no_gpu(), reason="needs a machine without a CUDA device")
 def test_no_cpu_fallback_without_a_gpu():
     from rtldavis_b200 import dsp, protocol
+    # the single-stream mirror creates its device handle at the first call (the reference builds
+    # a Demodulator in a parent process that must stay free of CUDA before it forks its worker)
+    dem = dsp.Demodulator(protocol.new_packet_config(14))
     with pytest.raises(Exception) as e:
-        dsp.Demodulator(protocol.new_packet_config(14))
+        dem.demodulate(np.full(2 * 8192, 127, dtype=np.uint8))
     assert not isinstance(e.value, (AttributeError, TypeError, NameError))
+    with pytest.raises(Exception):
+        dem.discriminated
     with pytest.raises(Exception):
         dsp.BatchDemodulator(protocol.new_packet_config(14), 4)
 
