@@ -48,7 +48,8 @@ SAMPLE_STREAMS, SAMPLE_BLOCKS = 8, 41          # the bounded sample the CPU legs
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=None,
+                    help="timed steps (default: 400 = a timed region of >= 1 s; reference arm: 20)")
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="graft", choices=["graft", "reference"])
     ap.add_argument("--streams", type=int, default=1024, help="streams per GPU")
@@ -65,7 +66,10 @@ def parse_args():
                          "wave buffers (BASELINE config 5: --streams 8192 --e2e-waves 8)")
     ap.add_argument("--e2e-steps", type=int, default=0, help="steps of the end-to-end leg (default: --steps)")
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
-    return ap.parse_args()
+    a = ap.parse_args()
+    if a.steps is None:
+        a.steps = 400 if a.impl == "graft" else 20
+    return a
 
 
 def workload_name(a):
@@ -140,11 +144,11 @@ def cpu_reference_rate(sample_iq: np.ndarray, seconds: float, cores: int):
     return samples / busy / 1e6, samples, wall, sum(r[2] for r in res)
 
 
-def cpu_sample_text(cores, seconds, kind):
+def cpu_sample_text(cores, seconds, kind, source="bytes of the GPU arm's own device generator, same seed"):
     what = ("the unmodified rtldavis Parser: demodulator.demodulate + parse (oracle/_ref)" if kind == "ref"
             else "the oracle's literal restatement of dsp.Demodulator (per-sample quantize kept)")
-    return (f"first {SAMPLE_STREAMS} streams x {SAMPLE_BLOCKS} blocks of this workload (bytes of the GPU arm's own "
-            f"device generator, same seed); {cores} processes x ~{seconds:g} s, block by block through {what}")
+    return (f"first {SAMPLE_STREAMS} streams x {SAMPLE_BLOCKS} blocks of this workload ({source}); "
+            f"{cores} processes x ~{seconds:g} s, block by block through {what}")
 
 
 def c_port_rate(sample_iq: np.ndarray, cores: int):
@@ -162,20 +166,6 @@ def usable_cores() -> int:
         return max(1, len(os.sched_getaffinity(0)))
     except AttributeError:
         return os.cpu_count() or 1
-
-
-def device_sample(a, n_streams, n_blocks, local=0, seed=None):
-    """The first `n_streams` streams x `n_blocks` blocks of the bench workload as host bytes,
-    produced by the device generator the GPU arm uses (input generation only)."""
-    import torch
-    from rtldavis_b200 import _lib
-    L = _lib.load()
-    n_samples = a.blocks * BLOCK
-    buf = torch.empty((n_streams, 2 * n_samples), dtype=torch.uint8, device=f"cuda:{local}")
-    _lib.check(L.davis_synth_fill(buf.data_ptr(), n_streams, 2 * n_samples, n_samples,
-                                  a.seed if seed is None else seed, a.packets, a.snr, 3000.0, 50.0, local, None))
-    torch.cuda.synchronize(local)
-    return buf[:, : 2 * BLOCK * n_blocks].cpu().numpy()
 
 
 # ---------------------------------------------------------------------------
@@ -266,15 +256,16 @@ def run_reference(a):
         return 0
     cores = usable_cores()
     kind = cpu_kind()
-    input_note = "device generator (davis_synth_fill), the GPU arm's seed; input generation only, not timed"
-    try:
-        iq = device_sample(a, SAMPLE_STREAMS, min(a.blocks, SAMPLE_BLOCKS))
-    except Exception as e:                      # no CUDA device: the numpy generator, same signal model
-        from rtldavis_b200 import synth
-        iq, _ = synth.make_batch(SAMPLE_STREAMS, min(a.blocks, SAMPLE_BLOCKS) * BLOCK,
-                                 max(1, a.packets * SAMPLE_BLOCKS // 328), a.snr, seed0=a.seed,
-                                 df_range_hz=3000.0, ppm_range=50.0)
-        input_note = f"numpy generator rtldavis_b200.synth (no CUDA device: {type(e).__name__})"
+    # Nothing of the product runs in this arm: the sample comes from the numpy generator (same
+    # signal model, packet density, SNR and offsets as the GPU arm's device generator), so this
+    # process never loads libdavis_b200.so and its workers fork from a process without CUDA.
+    from rtldavis_b200 import synth
+    sample_blocks = min(a.blocks, SAMPLE_BLOCKS)
+    iq, _ = synth.make_batch(SAMPLE_STREAMS, sample_blocks * BLOCK,
+                             max(1, a.packets * sample_blocks // max(a.blocks, 1)), a.snr, seed0=a.seed,
+                             df_range_hz=3000.0, ppm_range=50.0)
+    input_note = ("numpy generator rtldavis_b200.synth.make_batch (the signal model of the GPU arm's device "
+                  "generator: same packet density, SNR, +-3 kHz, +-50 ppm); no CUDA library in this process")
     per_step = max(1.0, min(a.cpu_seconds, 150.0 / max(1, a.steps + a.warmup)))  # whole run <= ~2.5 min
     rates = []
     for i in range(a.warmup + a.steps):
@@ -291,7 +282,8 @@ def run_reference(a):
         "data": "synthetic",
         "config": config_dict(a),
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": kind,
-                         "sample": cpu_sample_text(cores, per_step, kind), "samples_per_step": samples,
+                         "sample": cpu_sample_text(cores, per_step, kind, "numpy generator, same signal model and seed"),
+                         "samples_per_step": samples,
                          "input": input_note},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -465,15 +457,27 @@ def run_graft(a):
     # ---- parity: the first 8 streams of every rank against the C oracle, gathered through
     #      the sharding layer (fresh state, one batch; outside every timed region) ----
     from oracle import c_oracle as CO
-    n_chk = min(8, a.streams)
+
+    def oracle_records(rows_u8, local_ids, call0=0):
+        """Records of the C oracle for the given rows, numbered as the handle numbers them."""
+        rec = CO.batch_records(rows_u8, block=BLOCK)
+        if call0:
+            rec = rec[rec["call"] >= call0]
+        orc = np.zeros(len(rec), dtype=HIT_DTYPE)
+        for k in ("call", "index", "data", "crc_ok"):
+            orc[k] = rec[k]
+        orc["call"] -= call0
+        orc["stream"] = np.asarray(local_ids, dtype=np.uint32)[rec["stream"]]
+        return orc
+
+    # 63 streams from the front of the rank's shard and its very last one (the shard edge)
+    chk = sorted(set(range(min(63, a.streams))) | {a.streams - 1})
+    n_chk = len(chk)
     sds[0].reset()
     sds[0].submit(dev)
     mine = sds[0].fetch()
-    got_all = shard.gather_packets(mine[mine["stream"] < n_chk], sds[0].first_stream)
-    rec = CO.batch_records(dev[:n_chk].cpu().numpy(), block=BLOCK)
-    orc = np.zeros(len(rec), dtype=HIT_DTYPE)
-    for k in ("stream", "call", "index", "data", "crc_ok"):
-        orc[k] = rec[k]
+    got_all = shard.gather_packets(mine[np.isin(mine["stream"], chk)], sds[0].first_stream)
+    orc = oracle_records(dev[torch.tensor(chk, device=dev.device)].cpu().numpy(), chk)
     want_all = shard.gather_packets(orc, sds[0].first_stream)
     parity = None
     if rank == 0:
@@ -482,7 +486,7 @@ def run_graft(a):
                   "mismatch": 0 if g_rows == w_rows else max(1, len(set(g_rows) ^ set(w_rows))),
                   "crc_valid": sum(r[4] for r in w_rows),
                   "how": "fresh state, one batch through shard.ShardedDemodulator; records of the first "
-                         f"{n_chk} streams of every rank gathered with shard.gather_packets and compared "
+                         f"{n_chk - 1} streams and the last stream of every rank gathered with shard.gather_packets and compared "
                          "(stream, call, index, 10 bytes, CRC verdict, order) with oracle/davis_oracle.c"}
 
     # ---- end to end: pinned host input, H2D + records D2H inside the timed region ----
@@ -493,7 +497,7 @@ def run_graft(a):
             probe = shard.probe_h2d_weights(local)
             weights = probe
         waves = max(1, a.e2e_waves)
-        e_steps = a.e2e_steps or a.steps
+        e_steps = a.e2e_steps or min(a.steps, 20)        # ~0.1-0.2 s per step: 20 steps are >= 2 s
         mine_n = shard.partition(n_global, world, weights)[rank][1]
         per_wave = (mine_n + waves - 1) // waves
         wave_n = [min(per_wave, mine_n - w * per_wave) for w in range(waves) if mine_n - w * per_wave > 0]
@@ -511,16 +515,20 @@ def run_graft(a):
         from rtldavis_b200 import dsp
         handles = [dsp.BatchDemodulator(cfg, n, device=local, max_blocks=a.blocks) for n in wave_n]
 
+        last_views = [None] * len(wave_n)               # packet records of the last step, per wave
+
         def e2e_step():
             h2d = d2h = valid = 0
             for w, (bd2, n) in enumerate(zip(handles, wave_n)):
                 bd2.submit(ring[w % 2][:n])
                 h2 = bd2.fetch(copy=False)
+                last_views[w] = h2
                 st2 = bd2.stats()
                 h2d += int(st2.h2d_bytes); d2h += int(st2.d2h_bytes); valid += int(h2["crc_ok"].sum())
             return h2d, d2h, valid
 
-        for _ in range(max(1, min(a.warmup, 2))):
+        e_warm = max(1, min(a.warmup, 2))
+        for _ in range(e_warm):
             e2e_step()
         barrier()
         t0 = time.perf_counter()
@@ -529,6 +537,29 @@ def run_graft(a):
         torch.cuda.synchronize()
         mine_dt = time.perf_counter() - t0
         dt = all_max(mine_dt)
+        # Parity of what was just timed: the records the LAST timed step returned for eight
+        # streams of every wave (front, middle and end of the rank's share: the shard and
+        # pipeline-group edges) against the C oracle on the same pinned bytes.  The handles carry
+        # their state from step to step and every step feeds the same bytes, so the oracle is run
+        # over two passes of a row and its second pass is compared (the carried state is a halo of
+        # less than two blocks); call numbers are taken relative to the pass.
+        passes_before = e_warm + e_steps - 1
+        e_mis = e_rec = e_streams = 0
+        for w, n in enumerate(wave_n):
+            ids = sorted({i for i in (0, 1, 2, n // 2, n // 2 + 1, n - 3, n - 2, n - 1) if 0 <= i < n})
+            rows = ring[w % 2][ids]
+            two = np.concatenate([rows, rows], axis=1) if passes_before else rows
+            want_w = oracle_records(two, ids, call0=a.blocks if passes_before else 0)
+            got_w = last_views[w][np.isin(last_views[w]["stream"], ids)].copy()
+            got_w["call"] -= passes_before * a.blocks
+            g_rows, w_rows = _rows(got_w), _rows(want_w)
+            e_mis += 0 if g_rows == w_rows else max(1, len(set(g_rows) ^ set(w_rows)))
+            e_rec += len(w_rows)
+            e_streams += len(ids)
+        e2e_parity = {"streams": all_sum(e_streams), "records": all_sum(e_rec), "mismatch": all_sum(e_mis),
+                      "how": "records of the last timed end-to-end step (pinned host input through the host "
+                             "pipeline) for 8 streams per wave per rank -- first, middle, last of the rank's share "
+                             "-- against oracle/davis_oracle.c on the same bytes"}
         e2e_samples = n_global * n_samples
         e2e = {"value": e2e_samples * e_steps / dt / 1e6, "unit": UNIT,
                "h2d_bytes_per_step": all_sum(h2d), "d2h_bytes_per_step": all_sum(d2h),
@@ -536,7 +567,7 @@ def run_graft(a):
                "valid_packets_last_step": all_sum(valid),
                "streams_this_rank": mine_n, "waves": len(wave_n),
                "split": "uniform" if weights is None else "weighted by the probed host->device rate of every rank",
-               "h2d_probe_gbs": probe}
+               "h2d_probe_gbs": probe, "parity_check": e2e_parity}
         if world > 1:
             counts = [torch.zeros(1, dtype=torch.int64, device="cuda") for _ in range(world)]
             dist.all_gather(counts, torch.tensor([mine_n], dtype=torch.int64, device="cuda"))

@@ -169,18 +169,30 @@ def make_batch(n_streams: int, n_samples: int, n_packets: int, snr_db: float = 3
     return out, truth
 
 
+# The US-band hop sequence of the Davis protocol as rtldavis tabulates it (the 51 values of
+# Parser.hop_pattern, src/rtldavis/protocol.py:173-225): hop k of a transmitter is on channel
+# HOP_PATTERN_US[(hop0 + k) % 51] of Parser.channels (protocol.py:119-171).
+HOP_PATTERN_US = (0, 19, 41, 25, 8, 47, 32, 13, 36, 22, 3, 29, 44, 16, 5, 27, 38, 10, 49, 21, 2, 30, 42,
+                  14, 48, 7, 24, 34, 45, 1, 17, 39, 26, 9, 31, 50, 37, 12, 20, 33, 4, 43, 28, 15, 35, 6,
+                  40, 11, 23, 46, 18)
+assert sorted(HOP_PATTERN_US) == list(range(51))
+
+
 def make_hop_set(n_channels: int, n_samples: int, n_transmitters: int, hop_samples: int,
                  snr_db: float = 30.0, seed: int = 0, df_range_hz: float = 3000.0
                  ) -> Tuple[np.ndarray, List[List[Embedded]]]:
     """BASELINE config 3: ``n_channels`` parallel narrowband streams (one per channel
     of the hop set, src/rtldavis/protocol.py:119-171).  Transmitter t sends one packet
-    every ``hop_samples`` samples and moves to the next channel of its hop pattern
-    (a seeded permutation standing in for protocol.py:173-225, which is itself a
-    permutation of the channel indices) after each one, so every packet appears on
-    exactly one stream.  Each channel has a fixed residual carrier offset."""
+    every ``hop_samples`` samples and moves to the next channel of the hop pattern after
+    each one, so every packet appears on exactly one stream.  With the full set of 51
+    channels the pattern is the reference's own table (``HOP_PATTERN_US``, indexing
+    Parser.channels); a smaller set hops a seeded permutation.  Each channel has a fixed
+    residual carrier offset (the tuner's error on that channel) inside ``df_range_hz``."""
     rng = np.random.default_rng(seed)
     df = rng.uniform(-df_range_hz, df_range_hz, size=n_channels)
-    pattern = rng.permutation(n_channels)
+    pattern = rng.permutation(n_channels)              # drawn either way: keeps the seed's other draws
+    if n_channels == len(HOP_PATTERN_US):
+        pattern = np.asarray(HOP_PATTERN_US)
     x = np.zeros((n_channels, n_samples), dtype=np.complex128)
     truth: List[List[Embedded]] = [[] for _ in range(n_channels)]
     burst_len = BURST_BITS * SPS + 2
