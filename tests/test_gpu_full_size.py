@@ -124,6 +124,40 @@ def test_config2_1024_streams_10s_every_record(dsp, protocol):
     assert back >= 0.995 * n_streams * 40
 
 
+def test_config2_1024_streams_10s_from_pinned_host_memory(dsp, protocol):
+    """The end-to-end leg's path at full size: the same 1 024 x 10 s batch as
+    pinned HOST memory, so it goes through the handle's pipeline stages (groups of ~24 streams
+    cycling through three staging buffers) instead of being used in place.  Every record against
+    the C oracle on the same bytes, and against the device-resident call."""
+    import torch
+    _need_gb(14)
+    n_streams = 1024
+    buf, _ = _device_batch(n_streams, N_BLOCKS, 778, 20.0)
+    cfg = protocol.new_packet_config(14)
+    with dsp.BatchDemodulator(cfg, n_streams, max_blocks=N_BLOCKS) as bd:
+        bd.submit(buf)
+        on_device = bd.fetch()
+    pinned = torch.empty(buf.shape, dtype=torch.uint8, pin_memory=True)
+    pinned.copy_(buf)
+    torch.cuda.synchronize()
+    del buf
+    host = pinned.numpy()
+    with dsp.BatchDemodulator(cfg, n_streams, max_blocks=N_BLOCKS) as bd:
+        bd.submit(host)
+        hits = bd.fetch()
+        st = bd.stats()
+    assert st.h2d_bytes == host.size                       # every byte crossed the host link, once
+    want = CO.batch_records(host)
+    assert want.shape[0] > 100_000 and hits.shape[0] == want.shape[0]
+    for k in ("stream", "call", "index", "crc_ok"):
+        assert np.array_equal(hits[k], want[k]), k
+    assert np.array_equal(hits["data"], want["data"])
+    for k in ("stream", "call", "index", "data", "crc_ok", "position", "rssi", "snr"):
+        assert np.array_equal(hits[k], on_device[k]), k      # the two input paths agree to the last bit
+    print(f"config 2 from pinned host memory: {want.shape[0]} records equal to the oracle's and to the "
+          f"device-resident call's")
+
+
 # ---------------------------------------------------------------------------
 # config 3: the 51-channel hop set, 10 s, block by block and in ragged chunks
 # ---------------------------------------------------------------------------
