@@ -30,7 +30,11 @@
 using namespace davis;
 #define CK(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { printf("%s: %s\n", #x, cudaGetErrorString(e_)); exit(1); } } while (0)
 
-constexpr int N = 48;                              // 16 columns x 3 tap limbs
+#ifndef LAB_L
+#define LAB_L 3
+#endif
+constexpr int L = LAB_L;                          // tap limbs (3: 24-bit taps, 2: 16-bit taps)
+constexpr int N = 16 * L;                          // 16 columns per limb
 constexpr int MMA_BYTES = 2048;                    // 1 024 samples
 #ifndef LAB_STAGE_MMAS
 #define LAB_STAGE_MMAS 4
@@ -122,7 +126,7 @@ k_drain(const uint8_t *__restrict__ iq, size_t row_bytes, int per_row, long long
 #pragma unroll
             for (int h = 0; h < NSTAGE; h++)
 #pragma unroll
-                for (int c = 0; c < 3; c++) tc_st16(t + h * STAGE_COLS + 16 * c, b0);
+                for (int c = 0; c < L; c++) tc_st16(t + h * STAGE_COLS + 16 * c, b0);
             asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
         }
         asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -194,9 +198,9 @@ k_drain(const uint8_t *__restrict__ iq, size_t row_bytes, int per_row, long long
             for (int h = 0; h < NSTAGE; h++) {
                 mbar_wait(smem_addr(&sm.tm_full[h]), (uint32_t)k & 1u);
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                uint32_t v[3][16];
+                uint32_t v[L][16];
 #pragma unroll
-                for (int c = 0; c < 3; c++) {
+                for (int c = 0; c < L; c++) {
                     if (SKIP == 0) tc_ld16(t0 + h * STAGE_COLS + 16 * c, v[c]);
                     else
 #pragma unroll
@@ -205,7 +209,7 @@ k_drain(const uint8_t *__restrict__ iq, size_t row_bytes, int per_row, long long
                 if (SKIP == 0) asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
                 if (BIAS) {
 #pragma unroll
-                    for (int c = 0; c < 3; c++) tc_st16(t0 + h * STAGE_COLS + 16 * c, bias);
+                    for (int c = 0; c < L; c++) tc_st16(t0 + h * STAGE_COLS + 16 * c, bias);
                     asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
                 }
                 asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -220,17 +224,22 @@ k_drain(const uint8_t *__restrict__ iq, size_t row_bytes, int per_row, long long
 #pragma unroll
                     for (int sidx = 0; sidx < 8; sidx++) {
                         const int hh = sidx >> 2, sp = sidx & 3;
-                        float f[2][3];
+                        float f[2][L];
 #pragma unroll
                         for (int comp = 0; comp < 2; comp++)
 #pragma unroll
-                            for (int l = 0; l < 3; l++) {
-                                const int col = 24 * hh + 8 * l + 2 * sp + comp;
+                            for (int l = 0; l < L; l++) {
+                                const int col = 8 * L * hh + 8 * l + 2 * sp + comp;
                                 const uint32_t w = v[col >> 4][col & 15];
                                 f[comp][l] = __uint_as_float(BIAS ? w : w + (0x4B400000u - 77u));
                             }
-                        z[sidx].x = f[0][0] + fmaf(f[0][1], 256.f, fmaf(f[0][2], 65536.f, -65793.f * 12582912.f));
-                        z[sidx].y = f[1][0] + fmaf(f[1][1], 256.f, fmaf(f[1][2], 65536.f, -65793.f * 12582912.f));
+                        if (L == 3) {
+                            z[sidx].x = f[0][0] + fmaf(f[0][1], 256.f, fmaf(f[0][L - 1], 65536.f, -65793.f * 12582912.f));
+                            z[sidx].y = f[1][0] + fmaf(f[1][1], 256.f, fmaf(f[1][L - 1], 65536.f, -65793.f * 12582912.f));
+                        } else {
+                            z[sidx].x = f[0][0] + fmaf(f[0][1], 256.f, -257.f * 12582912.f);
+                            z[sidx].y = f[1][0] + fmaf(f[1][1], 256.f, -257.f * 12582912.f);
+                        }
                     }
                     z[8].x = __shfl_down_sync(0xFFFFFFFFu, z[0].x, 1);
                     z[8].y = __shfl_down_sync(0xFFFFFFFFu, z[0].y, 1);
@@ -241,7 +250,7 @@ k_drain(const uint8_t *__restrict__ iq, size_t row_bytes, int per_row, long long
                     x = (x << 8) ^ acc;
                 } else {
 #pragma unroll
-                    for (int c = 0; c < 3; c++)
+                    for (int c = 0; c < L; c++)
 #pragma unroll
                         for (int e = 0; e < 16; e++) x ^= v[c][e];
                 }
@@ -290,7 +299,7 @@ int main(int argc, char **argv) {
     k_fill<<<sms * 8, 256>>>(iq, row * n_streams); CK(cudaDeviceSynchronize());
     printf("mma_drain_lab: %d streams x %d blocks = %.2f GB, %lld pieces of %d B, %d SMs, smem %zu B\n",
            n_streams, n_blocks, row * n_streams / 1e9, units, PIECE, sms, sizeof(Smem) + 256);
-    printf("stages: %d x %d MMAs (%d columns each), %d slots, %d drain warps\n", NSTAGE, STAGE_MMAS, STAGE_COLS, NSLOT, DRAIN_WARPS);
+    printf("L = %d limbs (N = %d); stages: %d x %d MMAs (%d columns each), %d slots, %d drain warps\n", L, N, NSTAGE, STAGE_MMAS, STAGE_COLS, NSLOT, DRAIN_WARPS);
     measure<false, 2>("copy + handshakes only (no MMA, no ld)", iq, row, per_row, units, sink, reps, sms);
     measure<false, 1>("copy + MMA stages, accumulators not read", iq, row, per_row, units, sink, reps, sms);
     measure<false, 0>("copy + MMA stages + tcgen05.ld drain", iq, row, per_row, units, sink, reps, sms);
